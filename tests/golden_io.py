@@ -1,0 +1,44 @@
+"""Loaders for the committed golden vectors (tests/golden, produced by make_golden.py
+from the live reference)."""
+import json
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+_EP_KEYS = ("cfg", "act", "rew", "done", "board", "turn", "legal", "obs", "winner", "cnt", "state4")
+
+
+def load_trajectories():
+    z = np.load(os.path.join(GOLDEN, "trajectories.npz"))
+    eps = []
+    for i in range(int(z["num_episodes"])):
+        e = {}
+        for k in _EP_KEYS:
+            name = "e%d_%s" % (i, k)
+            if name in z.files:
+                e[k] = z[name]
+        S, sudden, disk, seed, p_inv, mask_in_obs = [int(x) for x in e["cfg"]]
+        e.update(S=S, sudden=sudden, disk=disk, seed=seed, p_invalid=p_inv, mask_in_obs=mask_in_obs)
+        eps.append(e)
+    return eps
+
+
+def load_policies():
+    z = np.load(os.path.join(GOLDEN, "policies.npz"))
+    out = {}
+    for S in z["sizes"]:
+        S = int(S)
+        out[S] = dict(board=z["s%d_board" % S], turn=z["s%d_turn" % S], choice=z["s%d_choice" % S])
+    return out
+
+
+def load_wrappers():
+    with open(os.path.join(GOLDEN, "wrappers.json")) as f:
+        return json.load(f)
+
+
+def load_perft():
+    with open(os.path.join(GOLDEN, "perft.json")) as f:
+        return {int(k): v for k, v in json.load(f).items()}
