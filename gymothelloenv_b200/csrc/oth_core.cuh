@@ -1,0 +1,471 @@
+// oth_core.cuh -- bitboard rules engine for S x S Othello, S compile-time (sm_100a).
+//
+// One colour = S*S bits in W = ceil(S*S/64) 64-bit words, bit a <-> action a = r*S + c
+// (reference geometry: othello.py:342,392-393).  Everything here lives in registers of
+// ONE thread; the kernels in oth_kernels.cuh map one thread to one env.
+//
+// Reference behaviour implemented (paths relative to the reference root):
+//   legal()      othello.py:273-343  get_num_killed_enemy / get_possible_actions
+//   flips()      othello.py:391-410  update_board
+//   env_step()   othello.py:412-501  step / set_player_turn / determine_winner / count_disks
+//   env_reset()  othello.py:256-271 + :62-64 (opening budget)
+//   greedy_pick  simple_policies.py:69-92
+//   maximin_pick simple_policies.py:111-163
+// The algorithm is NOT the reference's cell-by-cell ray walk: moves and flips come from
+// 8 directional Kogge-Stone occluded fills (shift + mask), popcounts give the scores.
+#pragma once
+#include <stdint.h>
+#include "../../include/othello_b200.h"
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef long long i64;
+
+#define OTH_DEV __device__ __forceinline__
+
+// ----------------------------------------------------------------------------------
+// geometry: compile-time masks
+// ----------------------------------------------------------------------------------
+constexpr u64 geo_word_full(int S, int wi) {
+    u64 m = 0;
+    for (int b = 0; b < 64; b++) {
+        int a = wi * 64 + b;
+        if (a < S * S) m |= 1ull << b;
+    }
+    return m;
+}
+// cells whose column is neither 0 nor S-1: the only cells a horizontal / diagonal run of
+// bracketed discs can occupy, and masking the propagator with it makes shifts wrap-free
+constexpr u64 geo_word_inner(int S, int wi) {
+    u64 m = 0;
+    for (int b = 0; b < 64; b++) {
+        int a = wi * 64 + b;
+        if (a < S * S) {
+            int c = a % S;
+            if (c != 0 && c != S - 1) m |= 1ull << b;
+        }
+    }
+    return m;
+}
+constexpr u64 geo_word_of_cells(int S, int wi, int a0, int a1, int a2, int a3) {
+    u64 m = 0;
+    int cells[4] = {a0, a1, a2, a3};
+    for (int k = 0; k < 4; k++)
+        if (cells[k] >= 0 && cells[k] / 64 == wi) m |= 1ull << (cells[k] % 64);
+    return m;
+}
+constexpr int geo_rounds(int S) {   // smallest R with 2^R - 1 >= S - 2 (longest bracketed run)
+    int r = 1;
+    while ((1 << r) - 1 < S - 2) r++;
+    return r;
+}
+
+template <int S, int WI>
+struct GeoWord {
+    static constexpr int c = S / 2;
+    static constexpr u64 full = geo_word_full(S, WI);
+    static constexpr u64 inner = geo_word_inner(S, WI);
+    // othello.py:256-263: WHITE (c-1,c-1),(c,c); BLACK (c,c-1),(c-1,c)
+    static constexpr u64 start_white = geo_word_of_cells(S, WI, (c - 1) * S + (c - 1), c * S + c, -1, -1);
+    static constexpr u64 start_black = geo_word_of_cells(S, WI, c * S + (c - 1), (c - 1) * S + c, -1, -1);
+    // BLACK's first legal set: (c-2,c-1),(c-1,c-2),(c,c+1),(c+1,c)
+    static constexpr u64 start_legal =
+        geo_word_of_cells(S, WI, (c - 2) * S + (c - 1), (c - 1) * S + (c - 2), c * S + (c + 1), (c + 1) * S + c);
+};
+
+template <int S>
+struct Geo {
+    static constexpr int N = S * S;
+    static constexpr int W = (N + 63) / 64;
+    static constexpr int ROUNDS = geo_rounds(S);
+    static_assert(S >= OTH_MIN_BOARD_SIZE && S <= 16, "board size out of range");
+};
+
+template <int W>
+struct BB {
+    u64 w[W];
+};
+
+#define BB_FOR(i) _Pragma("unroll") for (int i = 0; i < W; i++)
+
+template <int W> OTH_DEV BB<W> operator&(const BB<W> &a, const BB<W> &b) { BB<W> r; BB_FOR(i) r.w[i] = a.w[i] & b.w[i]; return r; }
+template <int W> OTH_DEV BB<W> operator|(const BB<W> &a, const BB<W> &b) { BB<W> r; BB_FOR(i) r.w[i] = a.w[i] | b.w[i]; return r; }
+template <int W> OTH_DEV BB<W> operator^(const BB<W> &a, const BB<W> &b) { BB<W> r; BB_FOR(i) r.w[i] = a.w[i] ^ b.w[i]; return r; }
+template <int W> OTH_DEV BB<W> andnot(const BB<W> &a, const BB<W> &b) { BB<W> r; BB_FOR(i) r.w[i] = a.w[i] & ~b.w[i]; return r; }
+template <int W> OTH_DEV bool any(const BB<W> &a) { u64 x = 0; BB_FOR(i) x |= a.w[i]; return x != 0; }
+template <int W> OTH_DEV int popc(const BB<W> &a) { int n = 0; BB_FOR(i) n += __popcll(a.w[i]); return n; }
+template <int W> OTH_DEV BB<W> bb_zero() { BB<W> r; BB_FOR(i) r.w[i] = 0; return r; }
+template <int W> OTH_DEV BB<W> bb_select(bool c, const BB<W> &a, const BB<W> &b) { BB<W> r; BB_FOR(i) r.w[i] = c ? a.w[i] : b.w[i]; return r; }
+template <int W> OTH_DEV BB<W> bb_bit(int a) {   // a in [0, 64*W)
+    BB<W> r;
+    BB_FOR(i) r.w[i] = (a >> 6) == i ? (1ull << (a & 63)) : 0ull;
+    return r;
+}
+template <int W> OTH_DEV bool bb_test(const BB<W> &x, int a) {
+    u64 v = 0;
+    BB_FOR(i) v = (a >> 6) == i ? x.w[i] : v;
+    return (v >> (a & 63)) & 1ull;
+}
+
+#define GEO_BB(NAME, FIELD)                                                        \
+    template <int S> OTH_DEV BB<Geo<S>::W> NAME() {                                \
+        BB<Geo<S>::W> r;                                                           \
+        r.w[0] = GeoWord<S, 0>::FIELD;                                             \
+        if constexpr (Geo<S>::W > 1) r.w[1] = GeoWord<S, 1>::FIELD;                \
+        if constexpr (Geo<S>::W > 2) r.w[2] = GeoWord<S, 2>::FIELD;                \
+        if constexpr (Geo<S>::W > 3) r.w[3] = GeoWord<S, 3>::FIELD;                \
+        return r;                                                                  \
+    }
+GEO_BB(geo_full, full)
+GEO_BB(geo_inner, inner)
+GEO_BB(geo_start_white, start_white)
+GEO_BB(geo_start_black, start_black)
+GEO_BB(geo_start_legal, start_legal)
+
+// whole-board shifts by a compile-time distance (towards higher / lower bit indices)
+template <int K, int W>
+OTH_DEV BB<W> shl(const BB<W> &a) {
+    constexpr int q = K / 64, b = K % 64;
+    BB<W> r;
+    BB_FOR(i) {
+        u64 hi = (i - q >= 0) ? a.w[(i - q >= 0) ? i - q : 0] : 0ull;
+        u64 lo = (i - q - 1 >= 0) ? a.w[(i - q - 1 >= 0) ? i - q - 1 : 0] : 0ull;
+        r.w[i] = (b == 0) ? hi : ((hi << b) | (lo >> ((64 - b) & 63)));
+    }
+    return r;
+}
+template <int K, int W>
+OTH_DEV BB<W> shr(const BB<W> &a) {
+    constexpr int q = K / 64, b = K % 64;
+    BB<W> r;
+    BB_FOR(i) {
+        u64 lo = (i + q < W) ? a.w[(i + q < W) ? i + q : 0] : 0ull;
+        u64 hi = (i + q + 1 < W) ? a.w[(i + q + 1 < W) ? i + q + 1 : 0] : 0ull;
+        r.w[i] = (b == 0) ? lo : ((lo >> b) | (hi << ((64 - b) & 63)));
+    }
+    return r;
+}
+template <int K, bool LEFT, int W>
+OTH_DEV BB<W> sh(const BB<W> &a) {
+    if constexpr (LEFT) return shl<K, W>(a);
+    else return shr<K, W>(a);
+}
+
+// Kogge-Stone occluded fill: gen plus every cell reachable from gen by stepping STEP in
+// one direction through cells of pro only.  ROUNDS doublings cover runs of S-2 discs.
+template <int S, int STEP, bool LEFT>
+OTH_DEV BB<Geo<S>::W> kfill(BB<Geo<S>::W> gen, BB<Geo<S>::W> pro) {
+    constexpr int R = Geo<S>::ROUNDS;
+    constexpr int W = Geo<S>::W;
+    gen = gen | (pro & sh<STEP, LEFT, W>(gen));
+    if constexpr (R > 1) {
+        pro = pro & sh<STEP, LEFT, W>(pro);
+        gen = gen | (pro & sh<2 * STEP, LEFT, W>(gen));
+    }
+    if constexpr (R > 2) {
+        pro = pro & sh<2 * STEP, LEFT, W>(pro);
+        gen = gen | (pro & sh<4 * STEP, LEFT, W>(gen));
+    }
+    if constexpr (R > 3) {
+        pro = pro & sh<4 * STEP, LEFT, W>(pro);
+        gen = gen | (pro & sh<8 * STEP, LEFT, W>(gen));
+    }
+    return gen;
+}
+
+template <int S, int STEP, bool LEFT>
+OTH_DEV BB<Geo<S>::W> dir_moves(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &pro) {
+    constexpr int W = Geo<S>::W;
+    BB<W> run = kfill<S, STEP, LEFT>(own, pro) & pro;   // bracket-able opponent runs next to own discs
+    return sh<STEP, LEFT, W>(run);
+}
+
+// othello.py:313-343: empty cells from which >=1 direction holds a run of opponent discs
+// closed by an own disc.
+template <int S>
+OTH_DEV BB<Geo<S>::W> legal(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
+    constexpr int W = Geo<S>::W;
+    const BB<W> inner = opp & geo_inner<S>();
+    BB<W> m = dir_moves<S, 1, true>(own, inner);
+    m = m | dir_moves<S, 1, false>(own, inner);
+    m = m | dir_moves<S, S, true>(own, opp);
+    m = m | dir_moves<S, S, false>(own, opp);
+    m = m | dir_moves<S, S + 1, true>(own, inner);
+    m = m | dir_moves<S, S + 1, false>(own, inner);
+    m = m | dir_moves<S, S - 1, true>(own, inner);
+    m = m | dir_moves<S, S - 1, false>(own, inner);
+    return andnot(m & geo_full<S>(), own | opp);
+}
+
+template <int S, int STEP, bool LEFT>
+OTH_DEV BB<Geo<S>::W> dir_flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &pro) {
+    constexpr int W = Geo<S>::W;
+    BB<W> flood = kfill<S, STEP, LEFT>(mv, pro);
+    BB<W> closed = sh<STEP, LEFT, W>(flood) & own;   // the cell after the run holds an own disc
+    return bb_select(any(closed), flood & pro, bb_zero<W>());
+}
+
+// othello.py:391-410: discs turned by placing an own disc on the single cell `mv`
+// (mv == 0 gives 0, which is how invalid moves stay branch-free).
+template <int S>
+OTH_DEV BB<Geo<S>::W> flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
+    constexpr int W = Geo<S>::W;
+    const BB<W> inner = opp & geo_inner<S>();
+    BB<W> f = dir_flips<S, 1, true>(mv, own, inner);
+    f = f | dir_flips<S, 1, false>(mv, own, inner);
+    f = f | dir_flips<S, S, true>(mv, own, opp);
+    f = f | dir_flips<S, S, false>(mv, own, opp);
+    f = f | dir_flips<S, S + 1, true>(mv, own, inner);
+    f = f | dir_flips<S, S + 1, false>(mv, own, inner);
+    f = f | dir_flips<S, S - 1, true>(mv, own, inner);
+    f = f | dir_flips<S, S - 1, false>(mv, own, inner);
+    return f;
+}
+
+// position of the n-th (0-based) set bit, n < popc(x)
+OTH_DEV int nth_bit64(u64 x, int n) {
+    int pos = 0;
+    u32 v = (u32)x;
+    int c = __popc(v);
+    if (n >= c) { n -= c; pos = 32; v = (u32)(x >> 32); }
+    c = __popc(v & 0xFFFFu); if (n >= c) { n -= c; pos += 16; v >>= 16; }
+    c = __popc(v & 0xFFu);   if (n >= c) { n -= c; pos += 8;  v >>= 8; }
+    c = __popc(v & 0xFu);    if (n >= c) { n -= c; pos += 4;  v >>= 4; }
+    c = __popc(v & 0x3u);    if (n >= c) { n -= c; pos += 2;  v >>= 2; }
+    c = v & 1u;              if (n >= c) { pos += 1; }
+    return pos;
+}
+template <int W>
+OTH_DEV int nth_bit(const BB<W> &x, int n) {
+    int base = 0;
+    u64 word = x.w[0];
+    bool found = false;
+    BB_FOR(i) {
+        if (i + 1 < W) {
+            int c = __popcll(x.w[i]);
+            if (!found) {
+                if (n < c) found = true;
+                else { n -= c; base = (i + 1) * 64; word = x.w[(i + 1 < W) ? i + 1 : 0]; }
+            }
+        }
+    }
+    return base + nth_bit64(word, n);
+}
+// lowest set bit index, x != 0
+template <int W>
+OTH_DEV int lowest_bit(const BB<W> &x) {
+    int r = 0;
+    bool found = false;
+    BB_FOR(i) {
+        if (!found && x.w[i]) { r = i * 64 + __ffsll((long long)x.w[i]) - 1; found = true; }
+    }
+    return r;
+}
+template <int W>
+OTH_DEV void clear_bit(BB<W> &x, int a) {
+    BB_FOR(i) x.w[i] &= ~((a >> 6) == i ? (1ull << (a & 63)) : 0ull);
+}
+
+// ----------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al., SC'11), counter-based: the stream of env `gid` is
+// block(ctr>>2)[ctr&3] with key = seed, counter = {block index, stream id, gid}.
+// ----------------------------------------------------------------------------------
+struct Philox4 { u32 v[4]; };
+OTH_DEV Philox4 philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1) {
+    const u32 M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        u32 hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        u32 hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        u32 n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += W0; k1 += W1;
+    }
+    Philox4 o;
+    o.v[0] = c0; o.v[1] = c1; o.v[2] = c2; o.v[3] = c3;
+    return o;
+}
+#define OTH_STREAM_ENV 0u      // opening budget, opening moves, fused random policy
+#define OTH_STREAM_POLICY 1u   // oth_policy(random)
+OTH_DEV u32 philox_draw(u64 seed, i64 gid, u32 stream, u32 ctr) {
+    Philox4 b = philox4x32_10(ctr >> 2, stream, (u32)(u64)gid, (u32)((u64)gid >> 32), (u32)seed, (u32)(seed >> 32));
+    u32 k = ctr & 3u;
+    return k == 0 ? b.v[0] : (k == 1 ? b.v[1] : (k == 2 ? b.v[2] : b.v[3]));
+}
+// uniform integer in [0, n) from 32 random bits (Lemire multiply-shift; bias <= n/2^32)
+OTH_DEV int bounded(u32 r, int n) { return (int)(((u64)r * (u64)(u32)n) >> 32); }
+
+// ----------------------------------------------------------------------------------
+// env in registers
+// ----------------------------------------------------------------------------------
+template <int S>
+struct EnvRegs {
+    BB<Geo<S>::W> black, white, legal;
+    u32 meta, ctr;
+};
+
+OTH_DEV int meta_rand_cnt(u32 m) { return (m >> OTH_META_RANDCNT_SHIFT) & 0xFF; }
+OTH_DEV int meta_rand_max(u32 m) { return (m >> OTH_META_RANDMAX_SHIFT) & 0xFF; }
+OTH_DEV int meta_winner(u32 m) { int c = (m >> OTH_META_WINNER_SHIFT) & 3; return c == 1 ? 1 : (c == 2 ? -1 : 0); }
+OTH_DEV u32 winner_code(int w) { return w > 0 ? 1u : (w < 0 ? 2u : 0u); }
+
+// OthelloBaseEnv.reset (othello.py:265-271) + opening budget (othello.py:62-64)
+template <int S>
+OTH_DEV void env_reset(EnvRegs<S> &e, u64 seed, i64 gid, int init_rand_steps) {
+    e.black = geo_start_black<S>();
+    e.white = geo_start_white<S>();
+    e.legal = geo_start_legal<S>();
+    int half = init_rand_steps / 2;
+    int budget = 0;
+    if (half > 0) {   // rnd.randint(0, init//2 + 1) * 2
+        budget = 2 * bounded(philox_draw(seed, gid, OTH_STREAM_ENV, e.ctr), half + 1);
+        e.ctr++;
+    }
+    e.meta = (u32)budget << OTH_META_RANDMAX_SHIFT;   // turn = BLACK, not terminated, winner 0, cnt 0
+}
+
+struct StepResult {
+    int reward;   // othello.py:444-461
+    int done;     // self.terminated
+    int winner;   // -1/0/+1 when done
+    int action;   // the action that was applied (or attempted)
+};
+
+// OthelloBaseEnv.step (othello.py:412-462) for a NON-terminated env.
+template <int S>
+OTH_DEV StepResult env_step(EnvRegs<S> &e, i64 action, int flags) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W;
+    const bool white_moves = e.meta & OTH_META_TURN_WHITE;
+    const int mover = white_moves ? 1 : -1;
+    BB<W> own = bb_select(white_moves, e.white, e.black);
+    BB<W> opp = bb_select(white_moves, e.black, e.white);
+
+    const bool in_range = (u64)action < (u64)N;
+    const int a = in_range ? (int)action : 0;
+    const bool valid = in_range && bb_test(e.legal, a);        // against the CACHED list (:417)
+    BB<W> mv = bb_select(valid, bb_bit<W>(a), bb_zero<W>());
+    BB<W> f = flips<S>(mv, own, opp);                          // update_board (:391-410)
+    own = own | f | mv;
+    opp = andnot(opp, f);
+
+    const bool sudden = !valid && (flags & OTH_F_SUDDEN_DEATH); // :427
+    const BB<W> vacant = andnot(geo_full<S>(), own | opp);
+    const bool full = !any(vacant);                             // :425-426
+    bool terminated = sudden || full;
+    bool next_white = white_moves;
+    BB<W> next_legal = e.legal;                                 // stale on sudden/full terminal (App. A.6)
+    if (!terminated) {
+        BB<W> lo = legal<S>(opp, own);                          // set_player_turn(-turn) (:436)
+        if (any(lo)) {
+            next_legal = lo;
+            next_white = !white_moves;
+        } else {
+            BB<W> lm = legal<S>(own, opp);                      // pass (:437-438)
+            next_legal = lm;
+            terminated = !any(lm);                              // double pass (:439-442)
+        }
+    }
+    const int own_cnt = popc(own), opp_cnt = popc(opp);
+    int winner = 0, reward = 0;
+    if (terminated) {
+        const int white_cnt = white_moves ? own_cnt : opp_cnt, black_cnt = white_moves ? opp_cnt : own_cnt;
+        winner = sudden ? -mover : (white_cnt > black_cnt ? 1 : (black_cnt > white_cnt ? -1 : 0)); // :473-501
+        if (flags & OTH_F_DISK_REWARD) {
+            reward = sudden ? -N : (opp_cnt == 0 ? N : own_cnt - opp_cnt);   // :446-459
+        } else {
+            reward = winner * mover;                                         // :461
+        }
+    }
+    e.white = bb_select(white_moves, own, opp);
+    e.black = bb_select(white_moves, opp, own);
+    e.legal = next_legal;
+    e.meta = (e.meta & 0xFFFFFF00u) | (next_white ? OTH_META_TURN_WHITE : 0u) |
+             (terminated ? OTH_META_TERMINATED : 0u) | (winner_code(winner) << OTH_META_WINNER_SHIFT);
+    StepResult r;
+    r.reward = reward; r.done = terminated; r.winner = winner; r.action = (int)action;
+    return r;
+}
+
+// RandomPolicy.get_action / the opening override: uniform over the cached list
+// (simple_policies.py:37-41, othello.py:70-72)
+template <int S>
+OTH_DEV int random_pick(const BB<Geo<S>::W> &moves, u32 rnd) {
+    int n = popc(moves);
+    return n > 0 ? nth_bit(moves, bounded(rnd, n)) : -1;
+}
+
+// GreedyPolicy.get_action (simple_policies.py:69-92): own disc count after each move =
+// own + flips + 1, np.argmax => most flips, lowest index on ties.
+template <int S>
+OTH_DEV int greedy_pick(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp, BB<Geo<S>::W> moves) {
+    constexpr int W = Geo<S>::W;
+    int best = -1, best_cnt = -1;
+    while (any(moves)) {
+        int a = lowest_bit(moves);
+        clear_bit(moves, a);
+        int cnt = popc(flips<S>(bb_bit<W>(a), own, opp));
+        if (cnt > best_cnt) { best_cnt = cnt; best = a; }
+    }
+    return best;
+}
+
+// MaxiMinPolicy.search below the root (simple_policies.py:111-155).  `pl` is to move.
+// Value = disc count of the searching side `me`; leaf when the depth budget is spent or
+// the side to move has no move (covers terminal boards and the forced-pass rule :139-144).
+template <int S, int D>
+struct MaxiMin {
+    static __device__ int value(const BB<Geo<S>::W> &pl, const BB<Geo<S>::W> &op, bool me_is_pl) {
+        constexpr int W = Geo<S>::W;
+        if constexpr (D == 0) {
+            return popc(me_is_pl ? pl : op);
+        } else {
+            BB<W> moves = legal<S>(pl, op);
+            if (!any(moves)) return popc(me_is_pl ? pl : op);
+            int best = me_is_pl ? -1 : 0x7FFFFFFF;
+            const int pl_cnt = popc(pl), op_cnt = popc(op);
+            while (any(moves)) {
+                int a = lowest_bit(moves);
+                clear_bit(moves, a);
+                BB<W> mv = bb_bit<W>(a);
+                BB<W> f = flips<S>(mv, pl, op);
+                int v;
+                if constexpr (D == 1) {      // children are leaves: count without expanding them
+                    int k = popc(f);
+                    v = me_is_pl ? pl_cnt + k + 1 : op_cnt - k;
+                } else {
+                    v = MaxiMin<S, D - 1>::value(andnot(op, f), pl | f | mv, !me_is_pl);
+                }
+                best = me_is_pl ? max(best, v) : min(best, v);
+            }
+            return best;
+        }
+    }
+    // root: iterate the CACHED list (env.possible_moves), first argmax (:151-155,157-163)
+    static __device__ int pick(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp, BB<Geo<S>::W> moves) {
+        constexpr int W = Geo<S>::W;
+        static_assert(D >= 1, "depth");
+        int best = -1, best_v = -1;
+        const int own_cnt = popc(own);
+        while (any(moves)) {
+            int a = lowest_bit(moves);
+            clear_bit(moves, a);
+            BB<W> mv = bb_bit<W>(a);
+            BB<W> f = flips<S>(mv, own, opp);
+            int v;
+            if constexpr (D == 1) v = own_cnt + popc(f) + 1;
+            else v = MaxiMin<S, D - 1>::value(andnot(opp, f), own | f | mv, false);
+            if (v > best_v) { best_v = v; best = a; }
+        }
+        return best;
+    }
+};
+
+template <int S>
+__device__ int policy_pick(int kind, int depth, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp,
+                           const BB<Geo<S>::W> &moves, u32 rnd) {
+    if (kind == OTH_POLICY_RANDOM) return random_pick<S>(moves, rnd);
+    if (kind == OTH_POLICY_GREEDY || depth <= 1) return greedy_pick<S>(own, opp, moves);   // README.md:54
+    if (depth == 2) return MaxiMin<S, 2>::pick(own, opp, moves);
+    if (depth == 3) return MaxiMin<S, 3>::pick(own, opp, moves);
+    return MaxiMin<S, 4>::pick(own, opp, moves);
+}

@@ -1,0 +1,439 @@
+// oth_kernels.cuh -- the sm_100a kernels of the Othello env engine for one board size S.
+//
+// Mapping: one thread = one env (bitboards in registers); 128-thread CTAs; state is SoA
+// in HBM so every state access is a coalesced 8-byte (or 4-byte) load/store per lane.
+// Dense outputs (obs planes, legal mask) are written WARP-COOPERATIVELY: each lane parks
+// its env's bitboards in a per-warp shared-memory slab, then the 32 lanes walk the
+// warp's contiguous output slab in 16-byte chunks so every store instruction covers
+// 512 contiguous bytes (st.global.v4), instead of 32 strided 64-byte rows.
+#pragma once
+#include <cuda_runtime.h>
+#include "oth_core.cuh"
+
+constexpr int OTH_BLOCK = 128;
+constexpr int OTH_WARPS = OTH_BLOCK / 32;
+
+enum { ROW_BLACK = 0, ROW_WHITE = 1, ROW_LEGAL = 2, ROW_ZERO = 3, ROW_ONES = 4, ROW_COUNT = 5 };
+#define OTH_LAYOUT_MASK_INTERNAL 6   // the dense legal_mask buffer, written with the same machinery
+
+template <int S>
+struct WarpStage {
+    u64 row[ROW_COUNT][Geo<S>::W][32];
+};
+
+__host__ __device__ constexpr int layout_planes(int layout) {
+    return layout == OTH_OBS_BOARD_MASK ? 2 : (layout == OTH_OBS_PLANES4 ? 4 : (layout == OTH_OBS_PLANES3 ? 3 : 1));
+}
+
+// which staged bitboard gives the +1 cells / the -1 cells of plane p
+template <int LAYOUT>
+OTH_DEV void plane_rows(int p, bool turn_white, bool quirk_empty, bool zero, int &pos, int &neg) {
+    neg = ROW_ZERO;
+    if constexpr (LAYOUT == OTH_OBS_BOARD) {                 // othello.py:363-369
+        pos = turn_white ? ROW_WHITE : ROW_BLACK;
+        neg = turn_white ? ROW_BLACK : ROW_WHITE;
+    } else if constexpr (LAYOUT == OTH_OBS_BOARD_MASK) {     // othello.py:370-376
+        pos = p == 0 ? (turn_white ? ROW_WHITE : ROW_BLACK) : ROW_LEGAL;
+        neg = p == 0 ? (turn_white ? ROW_BLACK : ROW_WHITE) : ROW_ZERO;
+    } else if constexpr (LAYOUT == OTH_OBS_PLANES4 || LAYOUT == OTH_OBS_PLANES3) {   // util.py:48-74
+        pos = p == 0 ? ROW_BLACK
+            : p == 1 ? ROW_WHITE
+            : p == 2 ? (turn_white ? ROW_ONES : ROW_ZERO)
+                     : (quirk_empty ? ROW_ZERO : ROW_LEGAL);
+    } else if constexpr (LAYOUT == OTH_OBS_ABSOLUTE) {       // board_state (othello.py:10-12)
+        pos = ROW_WHITE;
+        neg = ROW_BLACK;
+    } else {                                                 // dense legal mask
+        pos = ROW_LEGAL;
+    }
+    if (zero) { pos = ROW_ZERO; neg = ROW_ZERO; }
+}
+
+// 4 bits -> 4 bytes of 0/1 (bit i of n lands on bit 8*i: n*0x00204081 places it at
+// i, i+7, i+14, i+21 without carries; the mask keeps position 8*i)
+OTH_DEV u32 spread4(u32 n) { return (n * 0x00204081u) & 0x01010101u; }
+OTH_DEV u32 cells4_i8(u32 pn, u32 nn) { return spread4(nn) * 0xFFu + spread4(pn); }   // +1 / -1 bytes
+OTH_DEV u32 cell_f32(u32 pbit, u32 nbit) { return (pbit ? 0x3F800000u : 0u) | (nbit ? 0xBF800000u : 0u); }
+
+template <int S, int LAYOUT, int ES>
+__device__ __noinline__ void warp_write_planes(void *base, i64 env0, int nenv, const WarpStage<S> &st,
+                                               u32 turn_ballot, u32 quirk_ballot, u32 zero_ballot, int lane) {
+    constexpr int N = Geo<S>::N;
+    constexpr int P = layout_planes(LAYOUT);
+    constexpr int EPC = 16 / ES;                                   // elements per 16-byte chunk
+    constexpr int G = (ES == 1) ? (N % 16 == 0 ? 16 : (N % 4 == 0 ? 4 : 1)) : (N % 4 == 0 ? 4 : 1);
+    constexpr int GPC = EPC / G;                                   // groups per chunk
+    const int slab_bytes = nenv * P * N * ES;
+    const int nchunks = (slab_bytes + 15) >> 4;
+    char *slab = reinterpret_cast<char *>(base) + env0 * (i64)(P * N * ES);
+    for (int c = lane; c < nchunks; c += 32) {
+        u32 words[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int g = 0; g < GPC; g++) {
+            const int fe = c * EPC + g * G;                        // first element of the group in the slab
+            int e = fe / (P * N);
+            const int rem = fe - e * (P * N);
+            const int p = rem / N;
+            const int sq = rem - p * N;
+            e = min(e, 31);
+            int pos, neg;
+            plane_rows<LAYOUT>(p, (turn_ballot >> e) & 1u, (quirk_ballot >> e) & 1u, (zero_ballot >> e) & 1u, pos, neg);
+            const int wi = (Geo<S>::W == 1) ? 0 : (sq >> 6);
+            const u32 pb = (u32)(st.row[pos][wi][e] >> (sq & 63)) & ((1u << G) - 1u);
+            const u32 nb = (u32)(st.row[neg][wi][e] >> (sq & 63)) & ((1u << G) - 1u);
+            if constexpr (ES == 1) {
+                if constexpr (G == 16) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) words[k] = cells4_i8((pb >> (4 * k)) & 0xFu, (nb >> (4 * k)) & 0xFu);
+                } else if constexpr (G == 4) {
+                    words[g] = cells4_i8(pb, nb);
+                } else {
+                    words[g >> 2] |= ((pb ? 0x01u : 0u) | (nb ? 0xFFu : 0u)) << (8 * (g & 3));
+                }
+            } else {
+                if constexpr (G == 4) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) words[k] = cell_f32((pb >> k) & 1u, (nb >> k) & 1u);
+                } else {
+                    words[g] = cell_f32(pb, nb);
+                }
+            }
+        }
+        char *dst = slab + (i64)c * 16;
+        if (c * 16 + 16 <= slab_bytes) {
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(words[0], words[1], words[2], words[3]);
+        } else {   // ragged tail of the last warp
+            for (int b = 0; c * 16 + b < slab_bytes; b++) dst[b] = (char)(words[b >> 2] >> (8 * (b & 3)));
+        }
+    }
+}
+
+template <int S, int ES>
+OTH_DEV void warp_write_layout(int layout, void *base, i64 env0, int nenv, const WarpStage<S> &st, u32 turn_ballot,
+                               u32 quirk_ballot, u32 zero_ballot, int lane) {
+    switch (layout) {
+    case OTH_OBS_BOARD: warp_write_planes<S, OTH_OBS_BOARD, ES>(base, env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane); break;
+    case OTH_OBS_BOARD_MASK: warp_write_planes<S, OTH_OBS_BOARD_MASK, ES>(base, env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane); break;
+    case OTH_OBS_PLANES4: warp_write_planes<S, OTH_OBS_PLANES4, ES>(base, env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane); break;
+    case OTH_OBS_PLANES3: warp_write_planes<S, OTH_OBS_PLANES3, ES>(base, env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane); break;
+    case OTH_OBS_ABSOLUTE: warp_write_planes<S, OTH_OBS_ABSOLUTE, ES>(base, env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane); break;
+    default: break;
+    }
+}
+
+// stage this lane's env and write every requested dense output for the warp
+template <int S>
+OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, int flags, const oth_outputs &out,
+                        i64 warp_env0, i64 B, WarpStage<S> &st) {
+    constexpr int W = Geo<S>::W;
+    const int lane = threadIdx.x & 31;
+    BB_FOR(i) {
+        st.row[ROW_BLACK][i][lane] = active ? e.black.w[i] : 0ull;
+        st.row[ROW_WHITE][i][lane] = active ? e.white.w[i] : 0ull;
+        st.row[ROW_LEGAL][i][lane] = active ? e.legal.w[i] : 0ull;
+        st.row[ROW_ZERO][i][lane] = 0ull;
+        st.row[ROW_ONES][i][lane] = ~0ull;
+    }
+    const u32 turn_ballot = __ballot_sync(0xFFFFFFFFu, active && (e.meta & OTH_META_TURN_WHITE));
+    const u32 quirk_ballot = __ballot_sync(0xFFFFFFFFu, (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(e.legal) <= 1);
+    const u32 zero_ballot = __ballot_sync(0xFFFFFFFFu, zero_obs || !active);
+    __syncwarp();
+    if (warp_env0 < B) {
+        const int nenv = (int)min((i64)32, B - warp_env0);
+        if (out.obs != nullptr && out.obs_layout != OTH_OBS_NONE) {
+            if (out.obs_dtype == OTH_DTYPE_F32)
+                warp_write_layout<S, 4>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+            else
+                warp_write_layout<S, 1>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+        }
+        if (out.legal_mask != nullptr)
+            warp_write_planes<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+    }
+    __syncwarp();
+}
+
+template <int S>
+OTH_DEV void load_env(EnvRegs<S> &e, const oth_state &s, i64 i, i64 B) {
+    constexpr int W = Geo<S>::W;
+    BB_FOR(k) {
+        e.black.w[k] = s.black[k * B + i];
+        e.white.w[k] = s.white[k * B + i];
+        e.legal.w[k] = s.legal[k * B + i];
+    }
+    e.meta = s.meta[i];
+    e.ctr = s.ctr[i];
+}
+template <int S>
+OTH_DEV void store_env(const EnvRegs<S> &e, const oth_state &s, i64 i, i64 B) {
+    constexpr int W = Geo<S>::W;
+    BB_FOR(k) {
+        s.black[k * B + i] = e.black.w[k];
+        s.white[k * B + i] = e.white.w[k];
+        s.legal[k * B + i] = e.legal.w[k];
+    }
+    s.meta[i] = e.meta;
+    s.ctr[i] = e.ctr;
+}
+template <int S>
+OTH_DEV EnvRegs<S> empty_env() {
+    EnvRegs<S> e;
+    e.black = bb_zero<Geo<S>::W>(); e.white = e.black; e.legal = e.black;
+    e.meta = 0; e.ctr = 0;
+    return e;
+}
+
+// ---------------------------------------------------------------------------- reset
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_reset(oth_state s, i64 B, u64 seed, i64 base, int init_rand,
+                                                     int reset_rng, const uint8_t *only_where) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    if (only_where != nullptr && only_where[i] == 0) return;
+    EnvRegs<S> e;
+    e.ctr = reset_rng ? 0u : s.ctr[i];
+    env_reset<S>(e, seed, base + i, init_rand);
+    store_env<S>(e, s, i, B);
+}
+
+// -------------------------------------------------------------------------- observe
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_observe(oth_state s, i64 B, int flags, oth_outputs out) {
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    const bool active = i < B;
+    EnvRegs<S> e = empty_env<S>();
+    if (active) {
+        load_env<S>(e, s, i, B);
+        if (out.done) out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
+        if (out.player_turn) out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
+        if (out.winner) out.winner[i] = (int8_t)meta_winner(e.meta);
+    }
+    emit_dense<S>(e, active, false, flags, out, i - (threadIdx.x & 31), B, stage[threadIdx.x >> 5]);
+}
+
+// ----------------------------------------------------------------------------- step
+struct StepParams {
+    oth_state st;
+    i64 B;
+    int flags;
+    int action_source;
+    const i64 *actions;
+    u64 seed;
+    i64 base;
+    int init_rand;
+    oth_outputs out;
+};
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    const bool active = i < p.B;
+    EnvRegs<S> e = empty_env<S>();
+    bool zero_obs = false;
+    if (active) {
+        load_env<S>(e, p.st, i, p.B);
+        StepResult r;
+        r.reward = 0; r.done = 1; r.winner = 0; r.action = -1;
+        if (e.meta & OTH_META_TERMINATED) {
+            zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
+        } else {
+            i64 action = -1;
+            const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
+            if (opening || p.action_source == OTH_ACT_RANDOM) {
+                action = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                e.ctr++;
+                if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+            } else if (p.action_source == OTH_ACT_GREEDY) {
+                const bool wm = e.meta & OTH_META_TURN_WHITE;
+                action = greedy_pick<S>(bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal);
+            } else {
+                action = p.actions[i];
+            }
+            r = env_step<S>(e, action, p.flags);
+            if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+            store_env<S>(e, p.st, i, p.B);
+        }
+        if (p.out.reward) p.out.reward[i] = (float)r.reward;
+        if (p.out.done) p.out.done[i] = (uint8_t)r.done;
+        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
+        if (p.out.winner) p.out.winner[i] = (int8_t)r.winner;
+        if (p.out.actions_out) p.out.actions_out[i] = r.action;
+    }
+    emit_dense<S>(e, active, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+}
+
+// --------------------------------------------------------------------------- policy
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_policy(oth_state s, i64 B, int kind, int depth, u64 seed, u64 counter,
+                                                      i64 base, i64 *actions_out) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    EnvRegs<S> e;
+    load_env<S>(e, s, i, B);
+    int a = -1;
+    if (!(e.meta & OTH_META_TERMINATED) && any(e.legal)) {
+        const bool wm = e.meta & OTH_META_TURN_WHITE;
+        u32 rnd = 0;
+        if (kind == OTH_POLICY_RANDOM)
+            rnd = philox_draw(seed, base + i, OTH_STREAM_POLICY + (u32)(counter >> 32), (u32)counter);
+        a = policy_pick<S>(kind, depth, bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal, rnd);
+    }
+    actions_out[i] = a;
+}
+
+// -------------------------------------------------------------------------- rollout
+struct RolloutParams {
+    i64 B;
+    int flags;
+    oth_policy_spec black, white;
+    int init_rand;
+    int games_per_env;
+    u64 seed;
+    i64 base;
+    unsigned long long *tally;
+    int8_t *game_result;
+    int16_t *game_plies;
+    uint8_t *game_counts;
+    int16_t *trace;
+    int trace_stride;
+};
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    u32 t_black = 0, t_draw = 0, t_white = 0, t_plies = 0;
+    if (i < p.B) {
+        EnvRegs<S> e;
+        e.ctr = 0;
+        for (int g = 0; g < p.games_per_env; g++) {
+            const i64 game = i * p.games_per_env + g;
+            env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+            int ply = 0;
+            StepResult r;
+            r.done = 0; r.winner = 0;
+            while (!r.done) {
+                const bool wm = e.meta & OTH_META_TURN_WHITE;
+                const oth_policy_spec spec = wm ? p.white : p.black;
+                const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);
+                int a;
+                if (opening || spec.kind == OTH_POLICY_RANDOM) {
+                    a = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                    e.ctr++;
+                    if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+                } else {
+                    a = policy_pick<S>(spec.kind, spec.depth, bb_select(wm, e.white, e.black),
+                                       bb_select(wm, e.black, e.white), e.legal, 0u);
+                }
+                if (p.trace != nullptr && ply < p.trace_stride) p.trace[game * p.trace_stride + ply] = (int16_t)a;
+                r = env_step<S>(e, a, p.flags);
+                ply++;
+            }
+            t_plies += ply;
+            t_black += r.winner < 0;
+            t_draw += r.winner == 0;
+            t_white += r.winner > 0;
+            if (p.game_result) p.game_result[game] = (int8_t)r.winner;
+            if (p.game_plies) p.game_plies[game] = (int16_t)ply;
+            if (p.game_counts) {
+                p.game_counts[2 * game] = (uint8_t)popc(e.black);
+                p.game_counts[2 * game + 1] = (uint8_t)popc(e.white);
+            }
+        }
+    }
+    // warp tree-reduce, one atomic per counter per warp into the (NCCL send) buffer
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        t_black += __shfl_down_sync(0xFFFFFFFFu, t_black, o);
+        t_draw += __shfl_down_sync(0xFFFFFFFFu, t_draw, o);
+        t_white += __shfl_down_sync(0xFFFFFFFFu, t_white, o);
+        t_plies += __shfl_down_sync(0xFFFFFFFFu, t_plies, o);
+    }
+    if ((threadIdx.x & 31) == 0 && p.tally != nullptr) {
+        if (t_black) atomicAdd(&p.tally[0], (unsigned long long)t_black);
+        if (t_draw) atomicAdd(&p.tally[1], (unsigned long long)t_draw);
+        if (t_white) atomicAdd(&p.tally[2], (unsigned long long)t_white);
+        if (t_plies) atomicAdd(&p.tally[3], (unsigned long long)t_plies);
+    }
+}
+
+// ------------------------------------------------------------------------ set_board
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_set_board(oth_state s, i64 B, const int8_t *cells, const int8_t *perspective,
+                                                         const int8_t *turn, int recompute_legal, int clear_terminal) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W;
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    EnvRegs<S> e;
+    load_env<S>(e, s, i, B);
+    if (cells != nullptr) {
+        const int persp = perspective ? perspective[i] : 1;
+        e.black = bb_zero<W>();
+        e.white = bb_zero<W>();
+        for (int a = 0; a < N; a++) {
+            const int v = cells[i * N + a] * persp;     // othello.py:386-389
+            const u64 bit = 1ull << (a & 63);
+            BB_FOR(k) {
+                if ((a >> 6) == k) {
+                    if (v > 0) e.white.w[k] |= bit;
+                    if (v < 0) e.black.w[k] |= bit;
+                }
+            }
+        }
+    }
+    if (turn != nullptr) e.meta = (e.meta & ~OTH_META_TURN_WHITE) | (turn[i] > 0 ? OTH_META_TURN_WHITE : 0u);
+    if (clear_terminal) e.meta &= ~(OTH_META_TERMINATED | (3u << OTH_META_WINNER_SHIFT));
+    if (recompute_legal) {                               // set_player_turn (othello.py:464-466)
+        const bool wm = e.meta & OTH_META_TURN_WHITE;
+        e.legal = legal<S>(bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white));
+    }
+    store_env<S>(e, s, i, B);
+}
+
+// --------------------------------------------------------------------- host launchers
+struct OthSizeOps {
+    int S, W;
+    cudaError_t (*reset)(oth_state, i64, u64, i64, int, int, const uint8_t *, cudaStream_t);
+    cudaError_t (*observe)(oth_state, i64, int, oth_outputs, cudaStream_t);
+    cudaError_t (*step)(const StepParams &, cudaStream_t);
+    cudaError_t (*policy)(oth_state, i64, int, int, u64, u64, i64, i64 *, cudaStream_t);
+    cudaError_t (*rollout)(const RolloutParams &, cudaStream_t);
+    cudaError_t (*set_board)(oth_state, i64, const int8_t *, const int8_t *, const int8_t *, int, int, cudaStream_t);
+};
+
+static inline unsigned oth_grid(i64 B) { return (unsigned)((B + OTH_BLOCK - 1) / OTH_BLOCK); }
+
+template <int S>
+struct SizeLaunch {
+    static cudaError_t reset(oth_state s, i64 B, u64 seed, i64 base, int init_rand, int reset_rng,
+                             const uint8_t *only_where, cudaStream_t q) {
+        k_reset<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, seed, base, init_rand, reset_rng, only_where);
+        return cudaGetLastError();
+    }
+    static cudaError_t observe(oth_state s, i64 B, int flags, oth_outputs out, cudaStream_t q) {
+        k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
+        return cudaGetLastError();
+    }
+    static cudaError_t step(const StepParams &p, cudaStream_t q) {
+        k_step<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        return cudaGetLastError();
+    }
+    static cudaError_t policy(oth_state s, i64 B, int kind, int depth, u64 seed, u64 counter, i64 base, i64 *out,
+                              cudaStream_t q) {
+        k_policy<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, kind, depth, seed, counter, base, out);
+        return cudaGetLastError();
+    }
+    static cudaError_t rollout(const RolloutParams &p, cudaStream_t q) {
+        k_rollout<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        return cudaGetLastError();
+    }
+    static cudaError_t set_board(oth_state s, i64 B, const int8_t *cells, const int8_t *persp, const int8_t *turn,
+                                 int recompute, int clear_terminal, cudaStream_t q) {
+        k_set_board<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, cells, persp, turn, recompute, clear_terminal);
+        return cudaGetLastError();
+    }
+    static const OthSizeOps *ops() {
+        static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board};
+        return &o;
+    }
+};

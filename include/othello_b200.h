@@ -1,0 +1,177 @@
+/*
+ * othello_b200.h -- C ABI of libothello_b200.so, the B200 (sm_100a) Othello env engine.
+ *
+ * This is the drop-in boundary for the env hot path of omurammm/GymOthelloEnv.  The
+ * reference has no FFI of its own (it is pure Python); each entry point below names
+ * the reference interface it replaces (paths relative to the reference root).  The
+ * Python host package (gymothelloenv_b200/) binds these with ctypes and mirrors the
+ * reference's class API on top; INTEGRATION.md shows the stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless its name
+ *     ends in _host; buffers are owned by the caller (PyTorch's caching allocator) and
+ *     borrowed for the duration of one call;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL =
+ *     the legacy default stream) and never synchronises the host;
+ *   - return value: 0 on success, otherwise an OTH_ERR_* / cudaError_t-derived code;
+ *     oth_last_error() gives a thread-local message.  Nothing throws across the ABI;
+ *   - no global mutable state: safe from several host threads on distinct buffers.
+ *
+ * State layout (SoA, one slot per env, W = ceil(S*S/64) 64-bit words per colour):
+ *   black[w*B + i], white[w*B + i]   bit (r*S + c) of the S*S-bit board = cell (r, c),
+ *                                    i.e. bit a <-> action a (othello.py:342,392-393)
+ *   legal[w*B + i]                   the CACHED possible_moves set (othello.py:242,466),
+ *                                    including its stale value after a full-board /
+ *                                    sudden-death terminal
+ *   meta[i]  bit0 turn (0 = BLACK to move, 1 = WHITE)        (othello.py:239)
+ *            bit1 terminated                                  (othello.py:241)
+ *            bits2-3 winner: 0 none/draw, 1 WHITE, 2 BLACK    (othello.py:240)
+ *            bits8-15 rand_step_cnt, bits16-23 max_rand_steps (othello.py:50-51)
+ *   ctr[i]   number of Philox draws this env has consumed (RNG stream position)
+ */
+#ifndef OTHELLO_B200_H
+#define OTHELLO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OTH_ABI_VERSION 1
+#define OTH_MIN_BOARD_SIZE 4   /* othello.py:230 clamps to >= 4 */
+#define OTH_MAX_BOARD_SIZE 12
+
+typedef struct oth_state {
+    uint64_t *black;   /* [W][B] */
+    uint64_t *white;   /* [W][B] */
+    uint64_t *legal;   /* [W][B] */
+    uint32_t *meta;    /* [B] */
+    uint32_t *ctr;     /* [B] */
+} oth_state;
+
+/* meta word helpers */
+#define OTH_META_TURN_WHITE 0x1u
+#define OTH_META_TERMINATED 0x2u
+#define OTH_META_WINNER_SHIFT 2
+#define OTH_META_RANDCNT_SHIFT 8
+#define OTH_META_RANDMAX_SHIFT 16
+
+/* flags for oth_step / oth_rollout */
+#define OTH_F_SUDDEN_DEATH   0x01  /* sudden_death_on_invalid_move (othello.py:224,427) */
+#define OTH_F_DISK_REWARD    0x02  /* num_disk_as_reward (othello.py:225,446-459) */
+#define OTH_F_AUTO_RESET     0x04  /* finished envs restart inside the same step call */
+#define OTH_F_LEGACY_SINGLE_MOVE_PLANE 0x08 /* util.py:55: make_state legal plane is empty when exactly one move */
+
+/* observation layouts (plane count P, each plane S*S cells, env-major [B][P][S][S]) */
+#define OTH_OBS_NONE        0
+#define OTH_OBS_BOARD       1  /* P=1: mover's discs +1, opponent -1 (othello.py:363-369) */
+#define OTH_OBS_BOARD_MASK  2  /* P=2: + cached legal grid (possible_actions_in_obs, othello.py:370-376) */
+#define OTH_OBS_PLANES4     3  /* P=4: black, white, turn, legal (util.py:48-74) */
+#define OTH_OBS_PLANES3     4  /* P=3: black, white, turn (run_2agent.py:29-46) */
+#define OTH_OBS_ABSOLUTE    5  /* P=1: board_state itself, WHITE=+1 / BLACK=-1 (othello.py:10-12) */
+
+#define OTH_DTYPE_I8  0
+#define OTH_DTYPE_F32 1
+
+/* where oth_step takes its actions from */
+#define OTH_ACT_EXTERNAL 0   /* `actions` array, like env.step(a) */
+#define OTH_ACT_RANDOM   1   /* in-kernel RandomPolicy (simple_policies.py:37-41), Philox stream */
+#define OTH_ACT_GREEDY   2   /* in-kernel GreedyPolicy (simple_policies.py:69-92) */
+
+/* policy kinds for oth_policy / oth_rollout (util.py:28-45 create_policy) */
+#define OTH_POLICY_RANDOM  0
+#define OTH_POLICY_GREEDY  1
+#define OTH_POLICY_MAXIMIN 2
+#define OTH_MAX_SEARCH_DEPTH 4
+
+#define OTH_ERR_BAD_ARG        1001
+#define OTH_ERR_BAD_BOARD_SIZE 1002
+#define OTH_ERR_NULL_POINTER   1003
+#define OTH_ERR_CUDA           2000  /* + cudaError_t */
+
+/* outputs of one lockstep step / observe; any pointer may be NULL (not written) */
+typedef struct oth_outputs {
+    void    *obs;          /* [B][P][S*S] int8 or float32, see obs_layout / obs_dtype */
+    uint8_t *legal_mask;   /* [B][S*S] 0/1 bytes (torch.bool compatible): the cached possible_moves */
+    float   *reward;       /* [B] (othello.py:444-461), mover's perspective */
+    uint8_t *done;         /* [B] (othello.py:462 `self.terminated`) */
+    int8_t  *player_turn;  /* [B] -1 BLACK / +1 WHITE to move AFTER the call (othello.py:239) */
+    int8_t  *winner;       /* [B] result of a transition that ended a game: -1/0/+1, else 0 */
+    int64_t *actions_out;  /* [B] the action actually applied (after policy / random-opening override) */
+    int32_t obs_layout;    /* OTH_OBS_* */
+    int32_t obs_dtype;     /* OTH_DTYPE_* */
+} oth_outputs;
+
+typedef struct oth_policy_spec {
+    int32_t kind;    /* OTH_POLICY_* */
+    int32_t depth;   /* maximin search depth 1..OTH_MAX_SEARCH_DEPTH (simple_policies.py:101-103) */
+} oth_policy_spec;
+
+int         oth_abi_version(void);
+const char *oth_last_error(void);
+/* number of 64-bit words per colour for a board size, 0 if unsupported */
+int         oth_words_per_board(int board_size);
+
+/* OthelloBaseEnv.reset (othello.py:265-271) + SimpleOthelloEnv.reset's opening budget
+ * max_rand_steps = 2*U{0..init_rand_steps/2} (othello.py:62-64), for every env, or only
+ * for envs with only_where[i] != 0 when only_where is not NULL.  env_id_base + i is the
+ * global env id that keys the Philox stream (identical trajectories for any sharding).
+ * reset_rng != 0 rewinds ctr[i] to 0 (SimpleOthelloEnv.seed, othello.py:53-58). */
+int oth_reset(oth_state st, int64_t B, int board_size, uint64_t seed, int64_t env_id_base,
+              int init_rand_steps, int reset_rng, const uint8_t *only_where, void *stream);
+
+/* Writes obs / legal_mask / player_turn / done / winner for the CURRENT state without
+ * stepping: get_observation (othello.py:363-378), util.make_state (util.py:48-74),
+ * the possible_moves property (othello.py:91-93). reward/actions_out are ignored. */
+int oth_observe(oth_state st, int64_t B, int board_size, int flags, oth_outputs out, void *stream);
+
+/* One lockstep ply for every env: OthelloBaseEnv.step (othello.py:412-462) preceded by
+ * SimpleOthelloEnv.step's random-opening override (othello.py:68-73).
+ * action_source = OTH_ACT_EXTERNAL reads actions[i] (any int64: out-of-range or not in
+ * the cached list = invalid move => sudden death or forfeited turn, othello.py:417-428).
+ * Envs that are already terminated are a no-op reporting done=1, reward=0 and a zero
+ * observation (the reference raises ValueError, othello.py:415-416; the batched
+ * contract mirrors the worker's 'over' message, ppo_run_self_play.py:274). */
+int oth_step(oth_state st, int64_t B, int board_size, int flags, int action_source,
+             const int64_t *actions, uint64_t seed, int64_t env_id_base, int init_rand_steps,
+             oth_outputs out, void *stream);
+
+/* Batched policy.get_action for the side to move in every env
+ * (simple_policies.py:37-41 random, :69-92 greedy, :111-163 maximin).
+ * Terminated envs get -1.  `counter` selects the Philox block of the random policy's
+ * own stream (callers pass their step index). */
+int oth_policy(oth_state st, int64_t B, int board_size, oth_policy_spec spec, uint64_t seed,
+               uint64_t counter, int64_t env_id_base, int64_t *actions_out, void *stream);
+
+/* Fused tournament (run_2agent.py:92-203 with fixed colours; rule_base_game,
+ * ppo_run_self_play.py:371-441): every env plays games_per_env complete games, black
+ * policy vs white policy, first max_rand_steps plies uniformly random; no state is read
+ * or written, only tally[0..3] += {black wins, draws, white wins, plies} (atomics; the
+ * buffer is the NCCL all-reduce send buffer).  Optional per-game records for tests:
+ * game_result[g] (int8 winner), game_plies[g] (int16), game_counts[2g..] (uint8 black, white discs),
+ * trace[g*trace_stride + ply] (int16 action applied), with g = i*games_per_env + k. */
+int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec black, oth_policy_spec white,
+                int init_rand_steps, int games_per_env, uint64_t seed, int64_t env_id_base,
+                unsigned long long *tally, int8_t *game_result, int16_t *game_plies, uint8_t *game_counts,
+                int16_t *trace, int trace_stride, void *stream);
+
+/* set_board_state + set_player_turn (othello.py:380-389,464-466): dense cells [B][S*S]
+ * int8 seen from perspective[i] (+1: WHITE=+1, -1: negated), new turn[i] (-1/+1).
+ * recompute_legal != 0 refreshes the cached list (set_player_turn); 0 keeps it
+ * (set_board_state alone does not touch possible_moves). Clears terminated/winner only
+ * when clear_terminal != 0 (the reference never clears them outside reset). */
+int oth_set_board(oth_state st, int64_t B, int board_size, const int8_t *cells, const int8_t *perspective,
+                  const int8_t *turn, int recompute_legal, int clear_terminal, void *stream);
+
+/* Measurement helper: a dependency-limited LOP3/SHF/IADD3 stream on every SM; writes
+ * the number of thread-level integer instructions executed to *instr_out_host after the
+ * launch is enqueued (the count is static). Used by bench.py to measure the INT32-ALU
+ * roofline denominator that MEASURED_PEAKS.json does not contain. */
+int oth_int_alu_probe(uint32_t *sink, int blocks, int threads, int iters, uint64_t *instr_out_host, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OTHELLO_B200_H */
