@@ -8,7 +8,7 @@ One "step" = ONE lockstep ply of a batch of 2^20 8x8 envs per GPU: in-kernel ran
 policy (Philox) + rules step + auto-reset + the declared outputs (state, int8 obs
 (B,8,8), dense legal mask (B,64), reward f32, done, player_turn, winner, action) -- a
 single kernel launch (oth_step).  Envs are staggered over game phases (env i starts
-i mod 48 plies into a game) so every launch sees the natural mix of positions.
+i mod 60 plies into a game) so every launch sees the natural mix of positions.
 `value` = env steps/s with everything resident in HBM, all ranks (weak scaling: 2^20
 envs per GPU, no data-path collective; one 4-word all-reduce of counters at the end).
 `e2e` = the same step through HOST buffers (pinned actions in, obs/mask/reward/done out).
@@ -165,7 +165,7 @@ class ClockSampler(object):
 
 
 # ----------------------------------------------------------------------------- GPU arm
-def staggered_start(env, torch, phases=48):
+def staggered_start(env, torch, phases=60):
     """env i is advanced by (i mod phases) random plies."""
     env.reset()
     idx = torch.arange(env.num_envs, device=env.device) % phases

@@ -34,7 +34,7 @@ META_RANDMAX_SHIFT = 16
 
 EXPORTED_SYMBOLS = (
     "oth_abi_version", "oth_last_error", "oth_words_per_board", "oth_reset", "oth_observe", "oth_step",
-    "oth_policy", "oth_rollout", "oth_set_board", "oth_int_alu_probe",
+    "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
 )
 
 
@@ -92,6 +92,8 @@ def load():
     L.oth_set_board.restype = C.c_int
     L.oth_set_board.argtypes = [OthState, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                 C.c_void_p]
+    L.oth_update_board.restype = C.c_int
+    L.oth_update_board.argtypes = [OthState, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
     L.oth_int_alu_probe.restype = C.c_int
     L.oth_int_alu_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.c_void_p]
     if L.oth_abi_version() != 1:

@@ -147,6 +147,14 @@ OTH_API int oth_set_board(oth_state st, int64_t B, int board_size, const int8_t 
                                       (cudaStream_t)stream), "oth_set_board");
 }
 
+OTH_API int oth_update_board(oth_state st, int64_t B, int board_size, const int64_t *actions, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (actions == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions is null");
+    if (B == 0) return 0;
+    return cuda_result(ops->update_board(st, B, (const i64 *)actions, (cudaStream_t)stream), "oth_update_board");
+}
+
 // ---- INT32 ALU probe: 8 independent LOP3/SHF/IADD3 chains per thread -----------------
 #define PROBE_UNROLL 16
 __global__ void k_int_alu_probe(uint32_t *sink, int iters) {

@@ -390,6 +390,31 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_set_board(oth_state s, i64 B, con
     store_env<S>(e, s, i, B);
 }
 
+// --------------------------------------------------------------------- update_board
+// OthelloBaseEnv.update_board (othello.py:391-410) on its own: the side to move places a
+// disc on `action` and turns every bracketed run; no validity check, turn / cached list /
+// terminal flags untouched.
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_update_board(oth_state s, i64 B, const i64 *actions) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W;
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    const i64 action = actions[i];
+    if ((u64)action >= (u64)N) return;
+    EnvRegs<S> e;
+    load_env<S>(e, s, i, B);
+    const bool wm = e.meta & OTH_META_TURN_WHITE;
+    BB<W> own = bb_select(wm, e.white, e.black), opp = bb_select(wm, e.black, e.white);
+    const BB<W> mv = bb_bit<W>((int)action);
+    opp = andnot(opp, mv);                 // the reference overwrites the cell whatever it held
+    const BB<W> f = flips<S>(mv, own, opp);
+    own = own | f | mv;
+    opp = andnot(opp, f);
+    e.white = bb_select(wm, own, opp);
+    e.black = bb_select(wm, opp, own);
+    store_env<S>(e, s, i, B);
+}
+
 // --------------------------------------------------------------------- host launchers
 struct OthSizeOps {
     int S, W;
@@ -399,6 +424,7 @@ struct OthSizeOps {
     cudaError_t (*policy)(oth_state, i64, int, int, u64, u64, i64, i64 *, cudaStream_t);
     cudaError_t (*rollout)(const RolloutParams &, cudaStream_t);
     cudaError_t (*set_board)(oth_state, i64, const int8_t *, const int8_t *, const int8_t *, int, int, cudaStream_t);
+    cudaError_t (*update_board)(oth_state, i64, const i64 *, cudaStream_t);
 };
 
 static inline unsigned oth_grid(i64 B) { return (unsigned)((B + OTH_BLOCK - 1) / OTH_BLOCK); }
@@ -432,8 +458,12 @@ struct SizeLaunch {
         k_set_board<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, cells, persp, turn, recompute, clear_terminal);
         return cudaGetLastError();
     }
+    static cudaError_t update_board(oth_state s, i64 B, const i64 *actions, cudaStream_t q) {
+        k_update_board<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, actions);
+        return cudaGetLastError();
+    }
     static const OthSizeOps *ops() {
-        static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board};
+        static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board, &update_board};
         return &o;
     }
 };

@@ -64,24 +64,37 @@ def rollout(num_envs, black, white, board_size=8, initial_rand_steps=10, games_p
     return tally, rec
 
 
+def sharded_tally(num_units, local_fn, tally, group=None):
+    """Splits `num_units` (envs) in contiguous blocks over the ranks of `group`, calls
+    local_fn(first_global_id, count, tally) on this rank's block (it accumulates into the
+    4-word `tally` tensor) and sums the tallies with ONE all-reduce.  Host-side plumbing
+    only; also exercised on CPU/gloo by tests/test_host_logic.py."""
+    import torch.distributed as dist
+    rank, world = 0, 1
+    if dist.is_available() and dist.is_initialized():
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+    first, count = shard_range(num_units, rank, world)
+    if count > 0:
+        local_fn(first, count, tally)
+    if world > 1:
+        dist.all_reduce(tally, op=dist.ReduceOp.SUM, group=group)
+    return tally, world
+
+
 def play_tournament(black, white, num_games=100, board_size=8, initial_rand_steps=10, seed=0, device=None,
                     games_per_env=1, group=None):
     """README protocol (README.md:36-50): `black` (row) vs `white` (column), fixed colours,
     first <= initial_rand_steps plies random.  Sharded over torch.distributed ranks when a
     process group is initialised.  Returns a dict with black's wins/draws/losses, plies."""
-    import torch.distributed as dist
-    rank, world = 0, 1
-    if dist.is_available() and dist.is_initialized():
-        rank, world = dist.get_rank(group), dist.get_world_size(group)
     num_envs_total = (int(num_games) + games_per_env - 1) // games_per_env
-    first, count = shard_range(num_envs_total, rank, world)
     dev = require_cuda(device)
     tally = torch.zeros((4,), dtype=torch.int64, device=dev)
-    if count > 0:
+
+    def local(first, count, t):
         rollout(count, black, white, board_size=board_size, initial_rand_steps=initial_rand_steps,
-                games_per_env=games_per_env, seed=seed, env_id_base=first, device=dev, tally=tally)
-    if world > 1:
-        dist.all_reduce(tally, op=dist.ReduceOp.SUM, group=group)
+                games_per_env=games_per_env, seed=seed, env_id_base=first, device=dev, tally=t)
+
+    tally, world = sharded_tally(num_envs_total, local, tally, group)
     w, d, l, plies = [int(x) for x in tally.tolist()]
     return {"wins": w, "draws": d, "losses": l, "games": w + d + l, "plies": plies,
             "black": str(black), "white": str(white), "world_size": world}

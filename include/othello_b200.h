@@ -165,6 +165,11 @@ int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec black, oth
 int oth_set_board(oth_state st, int64_t B, int board_size, const int8_t *cells, const int8_t *perspective,
                   const int8_t *turn, int recompute_legal, int clear_terminal, void *stream);
 
+/* OthelloBaseEnv.update_board (othello.py:391-410) alone: the side to move places a disc on
+ * actions[i] and turns the bracketed runs; no validity check (a cell without brackets just
+ * receives the disc), turn / cached list / terminal flags untouched; out-of-range = no-op. */
+int oth_update_board(oth_state st, int64_t B, int board_size, const int64_t *actions, void *stream);
+
 /* Measurement helper: a dependency-limited LOP3/SHF/IADD3 stream on every SM; writes
  * the number of thread-level integer instructions executed to *instr_out_host after the
  * launch is enqueued (the count is static). Used by bench.py to measure the INT32-ALU

@@ -100,13 +100,27 @@ def _sample_actions(rng, legal, p_invalid, N):
     return a
 
 
-def _compare(env, orc, obs_layout, ctx):
+def _state_legal(env):
+    """The CACHED possible_moves set held in the state (not the per-step mask output)."""
+    words = env._legal.cpu().numpy().astype(np.uint64)          # [W, B]
+    bits = ((words[:, :, None] >> np.arange(64, dtype=np.uint64)[None, None, :]) & np.uint64(1)).astype(np.uint8)
+    return np.transpose(bits, (1, 0, 2)).reshape(words.shape[1], -1)[:, :env.num_cells]
+
+
+def _compare(env, orc, live_before, ctx):
+    """live_before: envs that were NOT finished before the call (None = all).  For a
+    finished env the step is a no-op whose dense outputs (obs, mask) are zero, while the
+    cached list in the state stays what the reference's possible_moves attribute holds."""
     snap = _dev_snapshot(env)
     board, legal, turn, term, winner, n_moves = orc.export()
     assert np.array_equal(snap["board"], board), ctx
     assert np.array_equal(snap["term"], term.astype(np.uint8)), ctx
     assert np.array_equal(snap["turn"], turn), ctx
-    assert np.array_equal(snap["legal"], legal), ctx
+    assert np.array_equal(_state_legal(env), legal), ctx
+    want_mask = legal.copy()
+    if live_before is not None:
+        want_mask[~live_before] = 0
+    assert np.array_equal(snap["legal"], want_mask), ctx
     return snap
 
 
@@ -123,7 +137,7 @@ def test_random_streams_vs_oracle(S, sudden, disk, p_invalid):
                obs_layout="board+mask")
     orc = oracle.OracleVec(B, S, sudden_death=sudden, disk_reward=disk)
     env.reset()
-    _compare(env, orc, "board+mask", "reset")
+    _compare(env, orc, None, "reset")
     steps = 0
     for t in range(N + 30):
         _, legal, _, term, _, _ = orc.export()
@@ -131,7 +145,7 @@ def test_random_streams_vs_oracle(S, sudden, disk, p_invalid):
         env.step(torch.from_numpy(acts).cuda())
         live = term == 0
         reward, done, _ = orc.step(acts)
-        snap = _compare(env, orc, "board+mask", "S=%d t=%d" % (S, t))
+        snap = _compare(env, orc, live, "S=%d t=%d" % (S, t))
         assert np.array_equal(snap["reward"].astype(np.int32), reward)
         assert np.array_equal(snap["done"], done)
         want_obs = orc.observe(with_mask=True)
