@@ -205,21 +205,58 @@ OTH_DEV BB<Geo<S>::W> dir_flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &ow
     return bb_select(any(closed), flood & pro, bb_zero<W>());
 }
 
+// ---- 8x8 flips by carry propagation -------------------------------------------------
+// For a ray of cells above the move (towards higher bit indices) with mask m:
+//   x = O | ~m ; t = x + 1 : the +1 carry ripples through every non-ray bit and through the
+//   contiguous opponent discs at the start of the ray and stops on the first ray cell that
+//   is not an opponent disc; t & ~x is that cell.  If it holds an own disc the run below it
+//   is bracketed: flipped = (stop - 1) & m.
+// The four rays towards lower indices are the same computation on bit-reversed boards.
+// Rays are mv * pattern (mv is a power of two, so the 64-bit IMADs are shifts that run on
+// the FMA pipe instead of the saturated ALU pipe).  Masking the opponent with the inner
+// columns for the horizontal / diagonal rays stops a run at the board edge (no wrap).
+OTH_DEV u64 ray_flips8(u64 m, u64 P, u64 O) {
+    const u64 x = O | ~m;
+    const u64 t = x + 1ull;
+    const u64 stop = t & ~x & P;                       // 0 or the single closing own disc
+    const u64 d = stop - (stop != 0ull ? 1ull : 0ull); // bits below the closing disc
+    return d & m;
+}
+OTH_DEV u64 flips8_up(u64 mv, u64 P, u64 O) {
+    const u64 Oi = O & 0x7E7E7E7E7E7E7E7Eull;
+    u64 f = ray_flips8(mv * 0x00000000000000FEull, P, Oi);          // +1
+    f |= ray_flips8(mv * 0x0101010101010100ull, P, O);             // +8
+    f |= ray_flips8(mv * 0x8040201008040200ull, P, Oi);            // +9
+    f |= ray_flips8(mv * 0x0002040810204080ull, P, Oi);            // +7
+    return f;
+}
+OTH_DEV u64 flips8(u64 mv, u64 P, u64 O) {
+    const u64 up = flips8_up(mv, P, O);
+    const u64 dn = flips8_up(__brevll(mv), __brevll(P), __brevll(O));
+    return up | __brevll(dn);
+}
+
 // othello.py:391-410: discs turned by placing an own disc on the single cell `mv`
 // (mv == 0 gives 0, which is how invalid moves stay branch-free).
 template <int S>
 OTH_DEV BB<Geo<S>::W> flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
     constexpr int W = Geo<S>::W;
-    const BB<W> inner = opp & geo_inner<S>();
-    BB<W> f = dir_flips<S, 1, true>(mv, own, inner);
-    f = f | dir_flips<S, 1, false>(mv, own, inner);
-    f = f | dir_flips<S, S, true>(mv, own, opp);
-    f = f | dir_flips<S, S, false>(mv, own, opp);
-    f = f | dir_flips<S, S + 1, true>(mv, own, inner);
-    f = f | dir_flips<S, S + 1, false>(mv, own, inner);
-    f = f | dir_flips<S, S - 1, true>(mv, own, inner);
-    f = f | dir_flips<S, S - 1, false>(mv, own, inner);
-    return f;
+    if constexpr (S == 8) {
+        BB<W> f;
+        f.w[0] = flips8(mv.w[0], own.w[0], opp.w[0]);
+        return f;
+    } else {
+        const BB<W> inner = opp & geo_inner<S>();
+        BB<W> f = dir_flips<S, 1, true>(mv, own, inner);
+        f = f | dir_flips<S, 1, false>(mv, own, inner);
+        f = f | dir_flips<S, S, true>(mv, own, opp);
+        f = f | dir_flips<S, S, false>(mv, own, opp);
+        f = f | dir_flips<S, S + 1, true>(mv, own, inner);
+        f = f | dir_flips<S, S + 1, false>(mv, own, inner);
+        f = f | dir_flips<S, S - 1, true>(mv, own, inner);
+        f = f | dir_flips<S, S - 1, false>(mv, own, inner);
+        return f;
+    }
 }
 
 // position of the n-th (0-based) set bit, n < popc(x)

@@ -121,35 +121,164 @@ OTH_DEV void warp_write_layout(int layout, void *base, i64 env0, int nenv, const
     }
 }
 
+// ---------------------------------------------------------------------------------
+// 8x8 fast path ("nibble staging").  The producer lane splits each 64-bit plane source
+// into 16 nibbles, one per byte (6 SIMD-in-register ops + 4 byte permutes per plane),
+// and parks them as one 16-byte row in shared memory.  A consumer lane then needs, per
+// 4 output cells, ONE LDS.U8 (the nibble), one IMAD (spread) and one LOP3 (mask): the
+// ALU pipe -- the binding unit of k_step, see profiles/ -- does ~1 op per 4 cells
+// instead of ~9, and the address of the 4 nibbles of int8 chunk c is simply 4*c.
+// ---------------------------------------------------------------------------------
+enum { NIB_POS0 = 0, NIB_POS1 = 1, NIB_POS2 = 2, NIB_POS3 = 3, NIB_NEG0 = 4, NIB_MASK = 5, NIB_ROWS = 6 };
+template <>
+struct WarpStage<8> {
+    uint4 nib[NIB_ROWS][32];
+};
+
+OTH_DEV uint4 nibble_bytes(u64 x) {
+    const u32 lo = (u32)x, hi = (u32)(x >> 32);
+    const u32 lo_e = lo & 0x0F0F0F0Fu, lo_o = (lo >> 4) & 0x0F0F0F0Fu;   // even / odd nibbles of cells 0..31
+    const u32 hi_e = hi & 0x0F0F0F0Fu, hi_o = (hi >> 4) & 0x0F0F0F0Fu;
+    uint4 r;
+    r.x = __byte_perm(lo_e, lo_o, 0x5140);   // n0 n1 n2 n3
+    r.y = __byte_perm(lo_e, lo_o, 0x7362);   // n4..n7
+    r.z = __byte_perm(hi_e, hi_o, 0x5140);
+    r.w = __byte_perm(hi_e, hi_o, 0x7362);
+    return r;
+}
+
+template <int LAYOUT, int ES>
+__device__ __noinline__ void fast8_write(void *base, i64 env0, int nenv, const WarpStage<8> &st, int lane) {
+    constexpr int P = layout_planes(LAYOUT);
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
+    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
+    char *slab = reinterpret_cast<char *>(base) + env0 * (i64)(P * 64 * ES);
+    if constexpr (ES == 1) {
+        const int nchunks = nenv * P * 4;                 // 16 cells per 16-byte chunk
+        for (int c = lane; c < nchunks; c += 32) {
+            int e, p, part;
+            if constexpr (P == 1) { e = c >> 2; p = 0; part = c & 3; }
+            else { part = c & 3; const int q = c >> 2; e = q / P; p = q - e * P; }
+            const unsigned char *src = rows + ((ROW0 + p) * 32 + e) * 16 + part * 4;
+            u32 w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) w[j] = spread4(src[j]);
+            if constexpr (HAS_NEG) {
+                if (p == 0) {
+                    const unsigned char *nsrc = rows + (NIB_NEG0 * 32 + e) * 16 + part * 4;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) w[j] = spread4(nsrc[j]) * 0xFFu + w[j];
+                }
+            }
+            *reinterpret_cast<uint4 *>(slab + (i64)c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    } else {
+        const int nchunks = nenv * P * 16;                // 4 cells (one nibble) per 16-byte chunk
+        for (int c = lane; c < nchunks; c += 32) {
+            const int k = c & 15, q = c >> 4;
+            int e, p;
+            if constexpr (P == 1) { e = q; p = 0; }
+            else { e = q / P; p = q - e * P; }
+            const u32 n = rows[((ROW0 + p) * 32 + e) * 16 + k];
+            u32 w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) w[j] = (n & (1u << j)) * (0x3F800000u >> j);
+            if constexpr (HAS_NEG) {
+                if (p == 0) {
+                    const u32 nn = rows[(NIB_NEG0 * 32 + e) * 16 + k];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) w[j] |= (nn & (1u << j)) * (0xBF800000u >> j);
+                }
+            }
+            *reinterpret_cast<uint4 *>(slab + (i64)c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+}
+
+template <int ES>
+OTH_DEV void fast8_write_layout(int layout, void *base, i64 env0, int nenv, const WarpStage<8> &st, int lane) {
+    switch (layout) {
+    case OTH_OBS_BOARD: fast8_write<OTH_OBS_BOARD, ES>(base, env0, nenv, st, lane); break;
+    case OTH_OBS_BOARD_MASK: fast8_write<OTH_OBS_BOARD_MASK, ES>(base, env0, nenv, st, lane); break;
+    case OTH_OBS_PLANES4: fast8_write<OTH_OBS_PLANES4, ES>(base, env0, nenv, st, lane); break;
+    case OTH_OBS_PLANES3: fast8_write<OTH_OBS_PLANES3, ES>(base, env0, nenv, st, lane); break;
+    case OTH_OBS_ABSOLUTE: fast8_write<OTH_OBS_ABSOLUTE, ES>(base, env0, nenv, st, lane); break;
+    default: break;
+    }
+}
+
+OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, int flags, const oth_outputs &out,
+                              i64 warp_env0, i64 B, WarpStage<8> &st) {
+    const int lane = threadIdx.x & 31;
+    const bool live = active && !zero_obs;
+    const bool tw = e.meta & OTH_META_TURN_WHITE;
+    const u64 black = live ? e.black.w[0] : 0ull, white = live ? e.white.w[0] : 0ull, lg = live ? e.legal.w[0] : 0ull;
+    const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    if (layout == OTH_OBS_BOARD || layout == OTH_OBS_BOARD_MASK) {           // othello.py:363-376
+        st.nib[NIB_POS0][lane] = nibble_bytes(tw ? white : black);
+        st.nib[NIB_NEG0][lane] = nibble_bytes(tw ? black : white);
+        if (layout == OTH_OBS_BOARD_MASK) st.nib[NIB_POS1][lane] = nibble_bytes(lg);
+    } else if (layout == OTH_OBS_ABSOLUTE) {
+        st.nib[NIB_POS0][lane] = nibble_bytes(white);
+        st.nib[NIB_NEG0][lane] = nibble_bytes(black);
+    } else if (layout == OTH_OBS_PLANES4 || layout == OTH_OBS_PLANES3) {     // util.py:48-74
+        st.nib[NIB_POS0][lane] = nibble_bytes(black);
+        st.nib[NIB_POS1][lane] = nibble_bytes(white);
+        const u32 t = (live && tw) ? 0x0F0F0F0Fu : 0u;
+        st.nib[NIB_POS2][lane] = make_uint4(t, t, t, t);
+        if (layout == OTH_OBS_PLANES4) {
+            const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && __popcll(lg) <= 1;   // util.py:55
+            st.nib[NIB_POS3][lane] = quirk ? z : nibble_bytes(lg);
+        }
+    }
+    if (out.legal_mask != nullptr) st.nib[NIB_MASK][lane] = nibble_bytes(lg);
+    __syncwarp();
+    if (warp_env0 < B) {
+        const int nenv = (int)min((i64)32, B - warp_env0);
+        if (layout != OTH_OBS_NONE) {
+            if (out.obs_dtype == OTH_DTYPE_F32) fast8_write_layout<4>(layout, out.obs, warp_env0, nenv, st, lane);
+            else fast8_write_layout<1>(layout, out.obs, warp_env0, nenv, st, lane);
+        }
+        if (out.legal_mask != nullptr) fast8_write<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+    }
+    __syncwarp();
+}
+
 // stage this lane's env and write every requested dense output for the warp
 template <int S>
 OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, int flags, const oth_outputs &out,
                         i64 warp_env0, i64 B, WarpStage<S> &st) {
-    constexpr int W = Geo<S>::W;
-    const int lane = threadIdx.x & 31;
-    BB_FOR(i) {
-        st.row[ROW_BLACK][i][lane] = active ? e.black.w[i] : 0ull;
-        st.row[ROW_WHITE][i][lane] = active ? e.white.w[i] : 0ull;
-        st.row[ROW_LEGAL][i][lane] = active ? e.legal.w[i] : 0ull;
-        st.row[ROW_ZERO][i][lane] = 0ull;
-        st.row[ROW_ONES][i][lane] = ~0ull;
-    }
-    const u32 turn_ballot = __ballot_sync(0xFFFFFFFFu, active && (e.meta & OTH_META_TURN_WHITE));
-    const u32 quirk_ballot = __ballot_sync(0xFFFFFFFFu, (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(e.legal) <= 1);
-    const u32 zero_ballot = __ballot_sync(0xFFFFFFFFu, zero_obs || !active);
-    __syncwarp();
-    if (warp_env0 < B) {
-        const int nenv = (int)min((i64)32, B - warp_env0);
-        if (out.obs != nullptr && out.obs_layout != OTH_OBS_NONE) {
-            if (out.obs_dtype == OTH_DTYPE_F32)
-                warp_write_layout<S, 4>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
-            else
-                warp_write_layout<S, 1>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+    if constexpr (S == 8) {
+        emit_dense_fast8(e, active, zero_obs, flags, out, warp_env0, B, st);
+    } else {
+        constexpr int W = Geo<S>::W;
+        const int lane = threadIdx.x & 31;
+        BB_FOR(i) {
+            st.row[ROW_BLACK][i][lane] = active ? e.black.w[i] : 0ull;
+            st.row[ROW_WHITE][i][lane] = active ? e.white.w[i] : 0ull;
+            st.row[ROW_LEGAL][i][lane] = active ? e.legal.w[i] : 0ull;
+            st.row[ROW_ZERO][i][lane] = 0ull;
+            st.row[ROW_ONES][i][lane] = ~0ull;
         }
-        if (out.legal_mask != nullptr)
-            warp_write_planes<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+        const u32 turn_ballot = __ballot_sync(0xFFFFFFFFu, active && (e.meta & OTH_META_TURN_WHITE));
+        const u32 quirk_ballot = __ballot_sync(0xFFFFFFFFu, (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(e.legal) <= 1);
+        const u32 zero_ballot = __ballot_sync(0xFFFFFFFFu, zero_obs || !active);
+        __syncwarp();
+        if (warp_env0 < B) {
+            const int nenv = (int)min((i64)32, B - warp_env0);
+            if (out.obs != nullptr && out.obs_layout != OTH_OBS_NONE) {
+                if (out.obs_dtype == OTH_DTYPE_F32)
+                    warp_write_layout<S, 4>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+                else
+                    warp_write_layout<S, 1>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+            }
+            if (out.legal_mask != nullptr)
+                warp_write_planes<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+        }
+        __syncwarp();
     }
-    __syncwarp();
 }
 
 template <int S>

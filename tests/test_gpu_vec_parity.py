@@ -298,12 +298,12 @@ def test_random_opening_budget_and_override():
     orc = oracle.OracleVec(B, S)
     for t in range(12):
         alive = ~env.terminated().cpu().numpy()
-        bogus = torch.full((B,), 0, dtype=torch.int64, device="cuda")   # a1 is never legal this early
+        bogus = torch.full((B,), -1, dtype=torch.int64, device="cuda")  # never a legal action
         env.step(bogus)
         got = env.actions_taken.cpu().numpy()
         overridden = alive & (t < mx)
         spent = alive & ~(t < mx)
-        assert (got[spent] == 0).all() and (got[~alive] == -1).all()
+        assert (got[spent] == -1).all() and (got[~alive] == -1).all() and (got[overridden] >= 0).all()
         _, _, valid = orc.step(got)
         assert valid[overridden].all()
         done = env.done.cpu().numpy()
