@@ -180,11 +180,45 @@ OTH_DEV BB<Geo<S>::W> dir_moves(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &p
     return sh<STEP, LEFT, W>(run);
 }
 
+// ---- 8x8 legal moves ---------------------------------------------------------------
+// East: adding the cells just east of own discs to the inner-column opponent mask makes
+// the carry ripple through each bracket-able run and land on the cell behind it (edge
+// columns are 0 in the mask, so a carry never leaves its row).  West = the same on
+// bit-reversed boards (BREV runs off the ALU pipe).  The three other axes use paired
+// fills that share the doubled propagator between the two opposite directions.
+template <int D>
+OTH_DEV u64 pair_moves8(u64 P, u64 m) {
+    u64 fl = m & (P << D), fr = m & (P >> D);
+    fl |= m & (fl << D);
+    fr |= m & (fr >> D);
+    const u64 pl = m & (m << D), pr = pl >> D;
+    fl |= pl & (fl << (2 * D));
+    fr |= pr & (fr >> (2 * D));
+    fl |= pl & (fl << (2 * D));
+    fr |= pr & (fr >> (2 * D));
+    return (fl << D) | (fr >> D);
+}
+OTH_DEV u64 legal8(u64 P, u64 O) {
+    const u64 Oi = O & 0x7E7E7E7E7E7E7E7Eull;
+    u64 moves = (Oi + ((P << 1) & Oi)) & ~Oi;
+    const u64 Pr = __brevll(P), Or = __brevll(Oi);
+    moves |= __brevll((Or + ((Pr << 1) & Or)) & ~Or);
+    moves |= pair_moves8<8>(P, O);
+    moves |= pair_moves8<7>(P, Oi);
+    moves |= pair_moves8<9>(P, Oi);
+    return moves & ~(P | O);
+}
+
 // othello.py:313-343: empty cells from which >=1 direction holds a run of opponent discs
 // closed by an own disc.
 template <int S>
 OTH_DEV BB<Geo<S>::W> legal(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
     constexpr int W = Geo<S>::W;
+    if constexpr (S == 8) {
+        BB<W> r;
+        r.w[0] = legal8(own.w[0], opp.w[0]);
+        return r;
+    }
     const BB<W> inner = opp & geo_inner<S>();
     BB<W> m = dir_moves<S, 1, true>(own, inner);
     m = m | dir_moves<S, 1, false>(own, inner);

@@ -147,6 +147,58 @@ OTH_DEV uint4 nibble_bytes(u64 x) {
     return r;
 }
 
+// Full warp (32 envs), fully unrolled: lane l owns, for every plane p and k = 0..3, the
+// (env, part) pair c' = 32k + l -> env c'>>2, 16-cell part c'&3.  Its nibbles sit at
+// row_p + 4c' in the stage and its 16 output bytes at env*P*64 + p*64 + part*16, so every
+// shared/global address is ONE per-lane base plus compile-time immediates: no index
+// arithmetic, no loop, no branch.  A quad of lanes writes 64 contiguous bytes.
+template <int LAYOUT, int ES>
+OTH_DEV void fast8_full(void *base, i64 env0, const WarpStage<8> &st, int lane) {
+    constexpr int P = layout_planes(LAYOUT);
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
+    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
+    if constexpr (ES == 1) {
+        const unsigned char *src = rows + ROW0 * 512 + lane * 4;
+        const unsigned char *nsrc = rows + NIB_NEG0 * 512 + lane * 4;
+        char *dst = reinterpret_cast<char *>(base) + env0 * (i64)(P * 64) + (lane >> 2) * (P * 64) + (lane & 3) * 16;
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                u32 w[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    w[j] = spread4(src[p * 512 + k * 128 + j]);
+                    if (HAS_NEG && p == 0) w[j] = spread4(nsrc[k * 128 + j]) * 0xFFu + w[j];
+                }
+                *reinterpret_cast<uint4 *>(dst + k * (8 * P * 64) + p * 64) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+    } else {
+        // f32: one nibble -> 4 floats = one 16-byte chunk; c' = 32k + l, k = 0..15 -> env c'>>4, nibble c'&15
+        const unsigned char *src = rows + ROW0 * 512 + lane;
+        const unsigned char *nsrc = rows + NIB_NEG0 * 512 + lane;
+        char *dst = reinterpret_cast<char *>(base) + env0 * (i64)(P * 256) + (lane >> 4) * (P * 256) + (lane & 15) * 16;
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+#pragma unroll 4
+            for (int k = 0; k < 16; k++) {
+                const u32 n = src[p * 512 + k * 32];
+                u32 w[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) w[j] = (n & (1u << j)) * (0x3F800000u >> j);
+                if (HAS_NEG && p == 0) {
+                    const u32 nn = nsrc[k * 32];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) w[j] |= (nn & (1u << j)) * (0xBF800000u >> j);
+                }
+                *reinterpret_cast<uint4 *>(dst + k * (2 * P * 256) + p * 256) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+        }
+    }
+}
+
 template <int LAYOUT, int ES>
 __device__ __noinline__ void fast8_write(void *base, i64 env0, int nenv, const WarpStage<8> &st, int lane) {
     constexpr int P = layout_planes(LAYOUT);
@@ -154,6 +206,10 @@ __device__ __noinline__ void fast8_write(void *base, i64 env0, int nenv, const W
     constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
     const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
     char *slab = reinterpret_cast<char *>(base) + env0 * (i64)(P * 64 * ES);
+    if (nenv == 32) {
+        fast8_full<LAYOUT, ES>(base, env0, st, lane);
+        return;
+    }
     if constexpr (ES == 1) {
         const int nchunks = nenv * P * 4;                 // 16 cells per 16-byte chunk
         for (int c = lane; c < nchunks; c += 32) {
@@ -237,11 +293,16 @@ OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, i
     __syncwarp();
     if (warp_env0 < B) {
         const int nenv = (int)min((i64)32, B - warp_env0);
-        if (layout != OTH_OBS_NONE) {
+        if (layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8 && nenv == 32) {
+            fast8_full<OTH_OBS_BOARD, 1>(out.obs, warp_env0, st, lane);          // the headline path, inlined
+        } else if (layout != OTH_OBS_NONE) {
             if (out.obs_dtype == OTH_DTYPE_F32) fast8_write_layout<4>(layout, out.obs, warp_env0, nenv, st, lane);
             else fast8_write_layout<1>(layout, out.obs, warp_env0, nenv, st, lane);
         }
-        if (out.legal_mask != nullptr) fast8_write<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+        if (out.legal_mask != nullptr) {
+            if (nenv == 32) fast8_full<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, st, lane);
+            else fast8_write<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+        }
     }
     __syncwarp();
 }
