@@ -42,3 +42,19 @@ def load_wrappers():
 def load_perft():
     with open(os.path.join(GOLDEN, "perft.json")) as f:
         return {int(k): v for k, v in json.load(f).items()}
+
+
+def load_selfplay():
+    """tests/golden/selfplay.npz (make_golden_selfplay.py): list of cases, each a dict with cfg fields,
+    `protagonist` (colour per game, shared by all workers), `test` = (games, wins) and per-call arrays."""
+    z = np.load(os.path.join(GOLDEN, "selfplay.npz"))
+    cases = []
+    for c in range(int(z["num_cases"])):
+        pre = "c%d_" % c
+        S, B, G, disk, seed, tg = [int(x) for x in z[pre + "cfg"]]
+        d = dict(S=S, B=B, games=G, disk=bool(disk), seed=seed, test_games=tg,
+                 protagonist=z[pre + "protagonist"], test=tuple(int(x) for x in z[pre + "test"]))
+        for k in ("game", "obs", "actions", "rewards", "dones", "types", "choices", "outputs", "masks", "bad_masks"):
+            d[k] = z[pre + k]
+        cases.append(d)
+    return cases
