@@ -18,6 +18,12 @@ F_SUDDEN_DEATH = 0x01
 F_DISK_REWARD = 0x02
 F_AUTO_RESET = 0x04
 F_LEGACY_SINGLE_MOVE_PLANE = 0x08
+F_ZERO_IF_TERMINATED = 0x10
+F_SP_FRESH_STATE = 0x20
+
+# self-play phase bits (OTH_SP_*) and categorical modes (OTH_CAT_*)
+SP_PENDING, SP_EMITTED, SP_FINISHED, SP_PREV_P = 0x01, 0x02, 0x04, 0x08
+CAT_SAMPLE, CAT_MODE, CAT_EVALUATE = 0, 1, 2
 
 OBS_NONE, OBS_BOARD, OBS_BOARD_MASK, OBS_PLANES4, OBS_PLANES3, OBS_ABSOLUTE = 0, 1, 2, 3, 4, 5
 OBS_PLANES = {OBS_NONE: 0, OBS_BOARD: 1, OBS_BOARD_MASK: 2, OBS_PLANES4: 4, OBS_PLANES3: 3, OBS_ABSOLUTE: 1}
@@ -35,6 +41,7 @@ META_RANDMAX_SHIFT = 16
 EXPORTED_SYMBOLS = (
     "oth_abi_version", "oth_last_error", "oth_words_per_board", "oth_reset", "oth_observe", "oth_step",
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
+    "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
 )
 
 
@@ -47,6 +54,12 @@ class OthOutputs(C.Structure):
     _fields_ = [("obs", C.c_void_p), ("legal_mask", C.c_void_p), ("reward", C.c_void_p), ("done", C.c_void_p),
                 ("player_turn", C.c_void_p), ("winner", C.c_void_p), ("actions_out", C.c_void_p),
                 ("obs_layout", C.c_int32), ("obs_dtype", C.c_int32)]
+
+
+class OthSelfPlay(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "protagonist", "phase", "sav_black", "sav_white", "sav_legal", "sav_meta", "sav_choices", "tr_action",
+        "tr_reward", "tr_done", "tr_type", "tr_outputs", "pend_outputs", "pend_action")]
 
 
 class OthPolicySpec(C.Structure):
@@ -96,6 +109,19 @@ def load():
     L.oth_update_board.argtypes = [OthState, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
     L.oth_int_alu_probe.restype = C.c_int
     L.oth_int_alu_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.c_void_p]
+    L.oth_selfplay_new_game.restype = C.c_int
+    L.oth_selfplay_new_game.argtypes = [OthState, OthSelfPlay, C.c_int64, C.c_int, C.c_uint64, C.c_int64, C.c_int,
+                                        C.c_uint64, C.c_void_p, C.c_void_p]
+    L.oth_selfplay_begin.restype = C.c_int
+    L.oth_selfplay_begin.argtypes = [OthState, OthSelfPlay, C.c_int64, C.c_int, C.c_int, OthOutputs, C.c_void_p,
+                                     C.c_void_p]
+    L.oth_selfplay_advance.restype = C.c_int
+    L.oth_selfplay_advance.argtypes = [OthState, OthSelfPlay, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_uint64, C.c_int64, C.c_int, OthOutputs,
+                                       C.c_void_p, C.c_void_p]
+    L.oth_masked_categorical.restype = C.c_int
+    L.oth_masked_categorical.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
+                                         C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     if L.oth_abi_version() != 1:
         raise OthelloB200Error("libothello_b200.so ABI version mismatch")
     _lib = L

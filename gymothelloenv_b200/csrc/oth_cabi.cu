@@ -155,6 +155,181 @@ OTH_API int oth_update_board(oth_state st, int64_t B, int board_size, const int6
     return cuda_result(ops->update_board(st, B, (const i64 *)actions, (cudaStream_t)stream), "oth_update_board");
 }
 
+// ---- PPO self-play protocol ----------------------------------------------------------
+static int check_selfplay(const oth_selfplay &sp) {
+    if (!sp.protagonist || !sp.phase || !sp.sav_black || !sp.sav_white || !sp.sav_legal || !sp.sav_meta ||
+        !sp.sav_choices || !sp.tr_action || !sp.tr_reward || !sp.tr_done || !sp.tr_type || !sp.tr_outputs ||
+        !sp.pend_outputs || !sp.pend_action)
+        return fail(OTH_ERR_NULL_POINTER, "null self-play pointer");
+    return 0;
+}
+
+OTH_API int oth_selfplay_new_game(oth_state st, oth_selfplay sp, int64_t B, int board_size, uint64_t seed,
+                                  int64_t env_id_base, int init_rand_steps, uint64_t game_index,
+                                  const int8_t *protagonist_in, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_selfplay(sp)) return rc;
+    if (init_rand_steps < 0 || init_rand_steps > 254) return fail(OTH_ERR_BAD_ARG, "init_rand_steps must be in 0..254");
+    if (B == 0) return 0;
+    return cuda_result(ops->selfplay_new_game(st, sp, B, seed, env_id_base, init_rand_steps, (u32)game_index,
+                                              protagonist_in, (cudaStream_t)stream), "oth_selfplay_new_game");
+}
+
+static int selfplay_launch(const OthSizeOps *ops, SelfPlayParams &p, void *stream, const char *what) {
+    if (p.need_count == nullptr) return fail(OTH_ERR_NULL_POINTER, "need_count is null");
+    cudaError_t e = cudaMemsetAsync(p.need_count, 0, sizeof(int), (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_result(e, what);
+    return cuda_result(ops->selfplay(p, (cudaStream_t)stream), what);
+}
+
+OTH_API int oth_selfplay_begin(oth_state st, oth_selfplay sp, int64_t B, int board_size, int flags, oth_outputs out,
+                               int32_t *need_count, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_selfplay(sp)) return rc;
+    if (int rc = check_outputs(out)) return rc;
+    if (B == 0) return 0;
+    SelfPlayParams p;
+    memset(&p, 0, sizeof(p));
+    p.st = st; p.sp = sp; p.B = B; p.flags = flags; p.mode = 0; p.out = out; p.need_count = need_count;
+    return selfplay_launch(ops, p, stream, "oth_selfplay_begin");
+}
+
+OTH_API int oth_selfplay_advance(oth_state st, oth_selfplay sp, int64_t B, int board_size, int flags,
+                                 const int64_t *actions, const float *value, const float *logp, const float *hidden,
+                                 uint64_t seed, int64_t env_id_base, int init_rand_steps, oth_outputs out,
+                                 int32_t *need_count, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_selfplay(sp)) return rc;
+    if (int rc = check_outputs(out)) return rc;
+    if (actions == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions is null");
+    if (init_rand_steps < 0 || init_rand_steps > 254) return fail(OTH_ERR_BAD_ARG, "init_rand_steps must be in 0..254");
+    if (B == 0) return 0;
+    SelfPlayParams p;
+    memset(&p, 0, sizeof(p));
+    p.st = st; p.sp = sp; p.B = B; p.flags = flags; p.mode = 1; p.actions = (const i64 *)actions;
+    p.value = value; p.logp = logp; p.hidden = hidden; p.seed = seed; p.base = env_id_base;
+    p.init_rand = init_rand_steps; p.out = out; p.need_count = need_count;
+    return selfplay_launch(ops, p, stream, "oth_selfplay_advance");
+}
+
+// ---- legal-move-restricted categorical (model.py:60-150,156-198) ---------------------
+// One warp per env; lane l holds actions l, l+32, ... (N <= 160).  float32, max-subtracted.
+#define OTH_STREAM_SAMPLE 3u
+constexpr int CAT_MAXK = 5;
+__global__ void __launch_bounds__(128) k_masked_categorical(const float *logits, const u64 *legal, i64 B, int N, int mode,
+                                                            const i64 *actions_in, u64 seed, u64 counter, i64 base,
+                                                            i64 *actions_out, float *logp_out) {
+    const i64 env = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= B) return;
+    const int K = (N + 31) >> 5;
+    const float NEG_INF = __int_as_float(0xFF800000u);
+    float x[CAT_MAXK];
+    bool ok[CAT_MAXK];
+    float m = NEG_INF;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const int a = 32 * k + lane;
+        ok[k] = false; x[k] = NEG_INF;
+        if (k < K && a < N) {
+            const u64 word = legal[(i64)(a >> 6) * B + env];
+            ok[k] = (word >> (a & 63)) & 1ull;
+            if (ok[k]) x[k] = logits[env * N + a];
+        }
+        m = fmaxf(m, x[k]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    u32 any_legal = 0;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) any_legal |= __ballot_sync(0xFFFFFFFFu, ok[k]);
+    if (any_legal == 0u) {                                   // model.py:71-73
+        if (lane == 0) {
+            if (actions_out) actions_out[env] = (mode == OTH_CAT_EVALUATE && actions_in) ? actions_in[env] : 0;
+            if (logp_out) logp_out[env] = 0.f;
+        }
+        return;
+    }
+    float ex[CAT_MAXK], s = 0.f;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) { ex[k] = ok[k] ? expf(x[k] - m) : 0.f; s += ex[k]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+    const float logZ = m + logf(s);
+    int chosen = -1;
+    if (mode == OTH_CAT_SAMPLE) {
+        const u32 r = philox_draw(seed, base + env, OTH_STREAM_SAMPLE + (u32)(counter >> 32), (u32)counter);
+        const float target = (float)(r >> 8) * (1.0f / 16777216.0f) * s;     // u in [0,1) times the mass
+        float acc = 0.f;
+        int last_legal = -1;
+#pragma unroll
+        for (int k = 0; k < CAT_MAXK; k++) {
+            float scan = ex[k];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const float t = __shfl_up_sync(0xFFFFFFFFu, scan, o);
+                if (lane >= o) scan += t;
+            }
+            const u32 hit = __ballot_sync(0xFFFFFFFFu, ok[k] && (acc + scan > target));
+            const u32 lg = __ballot_sync(0xFFFFFFFFu, ok[k]);
+            if (chosen < 0 && hit != 0u) chosen = 32 * k + __ffs(hit) - 1;
+            if (lg != 0u) last_legal = 32 * k + 31 - __clz(lg);
+            acc += __shfl_sync(0xFFFFFFFFu, scan, 31);
+        }
+        if (chosen < 0) chosen = last_legal;                 // rounding at the top of the CDF
+    } else if (mode == OTH_CAT_MODE) {
+        float best = NEG_INF;
+        int bi = 0x7FFFFFFF;
+#pragma unroll
+        for (int k = 0; k < CAT_MAXK; k++)
+            if (ok[k] && x[k] > best) { best = x[k]; bi = 32 * k + lane; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+            const int oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+        chosen = bi;
+    } else {
+        const i64 a = actions_in[env];
+        chosen = ((u64)a < (u64)N) ? (int)a : -1;
+    }
+    // log-probability of `chosen` (0 when it is not a legal choice, model.py:172-173)
+    float xc = 0.f;
+    bool legal_choice = false;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const float v = __shfl_sync(0xFFFFFFFFu, x[k], chosen & 31);
+        const bool g = __shfl_sync(0xFFFFFFFFu, (int)ok[k], chosen & 31);
+        if (chosen >= 0 && (chosen >> 5) == k) { xc = v; legal_choice = g; }
+    }
+    if (lane == 0) {
+        if (actions_out) actions_out[env] = (mode == OTH_CAT_EVALUATE) ? actions_in[env] : (i64)chosen;
+        if (logp_out) logp_out[env] = legal_choice ? (xc - logZ) : 0.f;
+    }
+}
+
+OTH_API int oth_masked_categorical(const float *logits, const uint64_t *legal, int64_t B, int board_size, int mode,
+                                   const int64_t *actions_in, uint64_t seed, uint64_t counter, int64_t env_id_base,
+                                   int64_t *actions_out, float *logp_out, void *stream) {
+    const OthSizeOps *ops = ops_for(board_size);
+    if (ops == nullptr) return fail(OTH_ERR_BAD_BOARD_SIZE, "board_size unsupported");
+    if (B < 0) return fail(OTH_ERR_BAD_ARG, "negative count");
+    if (logits == nullptr || legal == nullptr) return fail(OTH_ERR_NULL_POINTER, "logits / legal is null");
+    if (mode < OTH_CAT_SAMPLE || mode > OTH_CAT_EVALUATE) return fail(OTH_ERR_BAD_ARG, "bad mode");
+    if (mode == OTH_CAT_EVALUATE && actions_in == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions_in is null");
+    if (board_size * board_size > 32 * CAT_MAXK) return fail(OTH_ERR_BAD_BOARD_SIZE, "board too large for the sampler");
+    if (B == 0) return 0;
+    const unsigned grid = (unsigned)((B * 32 + 127) / 128);
+    k_masked_categorical<<<grid, 128, 0, (cudaStream_t)stream>>>(logits, (const u64 *)legal, B, board_size * board_size,
+                                                                 mode, (const i64 *)actions_in, seed, counter,
+                                                                 env_id_base, (i64 *)actions_out, logp_out);
+    return cuda_result(cudaGetLastError(), "oth_masked_categorical");
+}
+
 // ---- INT32 ALU probe: 8 independent LOP3/SHF/IADD3 chains per thread -----------------
 #define PROBE_UNROLL 16
 __global__ void k_int_alu_probe(uint32_t *sink, int iters) {

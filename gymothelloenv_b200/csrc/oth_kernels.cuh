@@ -264,12 +264,13 @@ OTH_DEV void fast8_write_layout(int layout, void *base, i64 env0, int nenv, cons
     }
 }
 
-OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, int flags, const oth_outputs &out,
-                              i64 warp_env0, i64 B, WarpStage<8> &st) {
+OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, bool zero_mask, int flags,
+                              const oth_outputs &out, i64 warp_env0, i64 B, WarpStage<8> &st) {
     const int lane = threadIdx.x & 31;
     const bool live = active && !zero_obs;
     const bool tw = e.meta & OTH_META_TURN_WHITE;
     const u64 black = live ? e.black.w[0] : 0ull, white = live ? e.white.w[0] : 0ull, lg = live ? e.legal.w[0] : 0ull;
+    const u64 lg_mask = (active && !zero_mask) ? e.legal.w[0] : 0ull;
     const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
     if (layout == OTH_OBS_BOARD || layout == OTH_OBS_BOARD_MASK) {           // othello.py:363-376
@@ -289,7 +290,7 @@ OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, i
             st.nib[NIB_POS3][lane] = quirk ? z : nibble_bytes(lg);
         }
     }
-    if (out.legal_mask != nullptr) st.nib[NIB_MASK][lane] = nibble_bytes(lg);
+    if (out.legal_mask != nullptr) st.nib[NIB_MASK][lane] = nibble_bytes(lg_mask);
     __syncwarp();
     if (warp_env0 < B) {
         const int nenv = (int)min((i64)32, B - warp_env0);
@@ -309,10 +310,10 @@ OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, i
 
 // stage this lane's env and write every requested dense output for the warp
 template <int S>
-OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, int flags, const oth_outputs &out,
-                        i64 warp_env0, i64 B, WarpStage<S> &st) {
+OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, bool zero_mask, int flags,
+                        const oth_outputs &out, i64 warp_env0, i64 B, WarpStage<S> &st) {
     if constexpr (S == 8) {
-        emit_dense_fast8(e, active, zero_obs, flags, out, warp_env0, B, st);
+        emit_dense_fast8(e, active, zero_obs, zero_mask, flags, out, warp_env0, B, st);
     } else {
         constexpr int W = Geo<S>::W;
         const int lane = threadIdx.x & 31;
@@ -326,6 +327,7 @@ OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, int fla
         const u32 turn_ballot = __ballot_sync(0xFFFFFFFFu, active && (e.meta & OTH_META_TURN_WHITE));
         const u32 quirk_ballot = __ballot_sync(0xFFFFFFFFu, (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(e.legal) <= 1);
         const u32 zero_ballot = __ballot_sync(0xFFFFFFFFu, zero_obs || !active);
+        const u32 zero_mask_ballot = __ballot_sync(0xFFFFFFFFu, zero_mask || !active);
         __syncwarp();
         if (warp_env0 < B) {
             const int nenv = (int)min((i64)32, B - warp_env0);
@@ -336,7 +338,7 @@ OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, int fla
                     warp_write_layout<S, 1>(out.obs_layout, out.obs, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
             }
             if (out.legal_mask != nullptr)
-                warp_write_planes<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_ballot, lane);
+                warp_write_planes<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, turn_ballot, quirk_ballot, zero_mask_ballot, lane);
         }
         __syncwarp();
     }
@@ -392,13 +394,15 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_observe(oth_state s, i64 B, int f
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
     const bool active = i < B;
     EnvRegs<S> e = empty_env<S>();
+    bool zero_obs = false;
     if (active) {
         load_env<S>(e, s, i, B);
         if (out.done) out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
         if (out.player_turn) out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
         if (out.winner) out.winner[i] = (int8_t)meta_winner(e.meta);
+        zero_obs = (flags & OTH_F_ZERO_IF_TERMINATED) && (e.meta & OTH_META_TERMINATED);
     }
-    emit_dense<S>(e, active, false, flags, out, i - (threadIdx.x & 31), B, stage[threadIdx.x >> 5]);
+    emit_dense<S>(e, active, zero_obs, false, flags, out, i - (threadIdx.x & 31), B, stage[threadIdx.x >> 5]);
 }
 
 // ----------------------------------------------------------------------------- step
@@ -450,7 +454,137 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
         if (p.out.winner) p.out.winner[i] = (int8_t)r.winner;
         if (p.out.actions_out) p.out.actions_out[i] = r.action;
     }
-    emit_dense<S>(e, active, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+    emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+}
+
+// ------------------------------------------------------------------------- self-play
+// The per-env machine behind PPOEnvs.step + subproc_worker (envs.py:188-227,
+// ppo_run_self_play.py:244-368): which protagonist tuple each env owes the learner and when
+// it is complete.  mode 0 = start of a round, mode 1 = one policy.act worth of plies.
+#define OTH_STREAM_PROTAGONIST 2u
+struct SelfPlayParams {
+    oth_state st;
+    oth_selfplay sp;
+    i64 B;
+    int flags;
+    int mode;
+    const i64 *actions;
+    const float *value, *logp, *hidden;
+    u64 seed;
+    i64 base;
+    int init_rand;
+    oth_outputs out;
+    int *need_count;
+};
+
+template <int S>
+OTH_DEV void sp_store_saved(const oth_selfplay &sp, i64 i, i64 B, const EnvRegs<S> &e, u32 meta) {
+    constexpr int W = Geo<S>::W;
+    BB_FOR(k) {
+        sp.sav_black[k * B + i] = e.black.w[k];
+        sp.sav_white[k * B + i] = e.white.w[k];
+        sp.sav_legal[k * B + i] = e.legal.w[k];
+    }
+    sp.sav_meta[i] = meta;
+}
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_selfplay(SelfPlayParams p) {
+    constexpr int W = Geo<S>::W;
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    const bool active = i < p.B;
+    EnvRegs<S> e = empty_env<S>();
+    bool need = false;
+    if (active) {
+        load_env<S>(e, p.st, i, p.B);
+        u32 ph = p.sp.phase[i];
+        bool emit = false, zero_tuple = false;
+        int tr_type = 0, tr_done = 0;
+        float tr_reward = 0.f, o0 = 0.f, o1 = 0.f, o2 = 0.f;
+        i64 tr_action = 0;
+        if (p.mode == 0) {
+            ph &= ~(u32)OTH_SP_EMITTED;
+            if (ph & OTH_SP_FINISHED) {                            // 'over' message (:273-274)
+                emit = true; zero_tuple = true; tr_type = 1; tr_done = 1;
+                BB_FOR(k) p.sp.sav_choices[k * p.B + i] = e.legal.w[k];   // env.possible_moves, stale list included
+            }
+        } else if (!(ph & OTH_SP_EMITTED)) {
+            const bool wm = e.meta & OTH_META_TURN_WHITE;
+            const int mover = wm ? 1 : -1, P = p.sp.protagonist[i];
+            const i64 a_pol = p.actions[i];
+            if (mover == P) {                                      // :285-290 / :325-330
+                if (!(ph & OTH_SP_PREV_P) || (p.flags & OTH_F_SP_FRESH_STATE))
+                    sp_store_saved<S>(p.sp, i, p.B, e, wm ? OTH_META_TURN_WHITE : 0u);
+                BB_FOR(k) p.sp.sav_choices[k * p.B + i] = e.legal.w[k];
+                o0 = p.value ? p.value[i] : 0.f; o1 = p.logp ? p.logp[i] : 0.f; o2 = p.hidden ? p.hidden[i] : 0.f;
+                p.sp.pend_action[i] = a_pol;
+                p.sp.pend_outputs[3 * i] = o0; p.sp.pend_outputs[3 * i + 1] = o1; p.sp.pend_outputs[3 * i + 2] = o2;
+                ph |= OTH_SP_PENDING;
+            }
+            i64 action = a_pol;
+            if (meta_rand_cnt(e.meta) < meta_rand_max(e.meta)) {   // opening override (othello.py:70-73)
+                action = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                e.ctr++;
+                e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+            }
+            const StepResult r = env_step<S>(e, action, p.flags);
+            const bool next_is_p = ((e.meta & OTH_META_TURN_WHITE) ? 1 : -1) == P;
+            if (mover == P) {
+                if (r.done || next_is_p) {                         // :292-295,313-317 / :332-335,350-354
+                    emit = true; tr_reward = (float)r.reward; tr_action = a_pol;
+                }
+                ph |= OTH_SP_PREV_P;
+            } else {
+                if (r.done || next_is_p) {
+                    if (ph & OTH_SP_PENDING) {                     // :305-309 / :344-347
+                        emit = true; tr_reward = (float)(-r.reward);
+                        tr_action = p.sp.pend_action[i];
+                        o0 = p.sp.pend_outputs[3 * i]; o1 = p.sp.pend_outputs[3 * i + 1]; o2 = p.sp.pend_outputs[3 * i + 2];
+                    } else if (r.done) {                           // :318-321
+                        emit = true; zero_tuple = true;
+                        BB_FOR(k) p.sp.sav_choices[k * p.B + i] = 0ull;
+                    }
+                }
+                ph &= ~(u32)OTH_SP_PREV_P;
+            }
+            tr_done = r.done;
+            if (r.done) ph |= OTH_SP_FINISHED;
+            store_env<S>(e, p.st, i, p.B);
+        }
+        if (emit) {
+            if (zero_tuple) { p.sp.sav_meta[i] = OTH_META_TERMINATED; tr_action = 0; tr_reward = 0.f; o0 = o1 = o2 = 0.f; tr_done = 1; }
+            p.sp.tr_action[i] = tr_action;
+            p.sp.tr_reward[i] = tr_reward;
+            p.sp.tr_done[i] = (uint8_t)tr_done;
+            p.sp.tr_type[i] = (uint8_t)tr_type;
+            p.sp.tr_outputs[3 * i] = o0; p.sp.tr_outputs[3 * i + 1] = o1; p.sp.tr_outputs[3 * i + 2] = o2;
+            ph = (ph | OTH_SP_EMITTED) & ~(u32)OTH_SP_PENDING;
+        }
+        p.sp.phase[i] = (uint8_t)ph;
+        need = !(ph & OTH_SP_EMITTED);
+        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
+        if (p.out.done) p.out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
+    }
+    const u32 nb = __ballot_sync(0xFFFFFFFFu, need);
+    if ((threadIdx.x & 31) == 0 && nb != 0u && p.need_count != nullptr) atomicAdd(p.need_count, __popc(nb));
+    const bool fin = active && (e.meta & OTH_META_TERMINATED);
+    emit_dense<S>(e, active, fin, fin, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+}
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_selfplay_new_game(oth_state s, oth_selfplay sp, i64 B, u64 seed, i64 base,
+                                                                 int init_rand, u32 game_index, const int8_t *protagonist_in) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    EnvRegs<S> e;
+    e.ctr = s.ctr[i];
+    env_reset<S>(e, seed, base + i, init_rand);
+    store_env<S>(e, s, i, B);
+    sp.phase[i] = 0;
+    sp.protagonist[i] = protagonist_in != nullptr
+        ? (int8_t)(protagonist_in[i] > 0 ? 1 : -1)
+        : (int8_t)((philox_draw(seed, base + i, OTH_STREAM_PROTAGONIST, game_index) & 1u) ? 1 : -1);   // :265-266
 }
 
 // --------------------------------------------------------------------------- policy
@@ -615,6 +749,8 @@ struct OthSizeOps {
     cudaError_t (*rollout)(const RolloutParams &, cudaStream_t);
     cudaError_t (*set_board)(oth_state, i64, const int8_t *, const int8_t *, const int8_t *, int, int, cudaStream_t);
     cudaError_t (*update_board)(oth_state, i64, const i64 *, cudaStream_t);
+    cudaError_t (*selfplay)(const SelfPlayParams &, cudaStream_t);
+    cudaError_t (*selfplay_new_game)(oth_state, oth_selfplay, i64, u64, i64, int, u32, const int8_t *, cudaStream_t);
 };
 
 static inline unsigned oth_grid(i64 B) { return (unsigned)((B + OTH_BLOCK - 1) / OTH_BLOCK); }
@@ -652,8 +788,18 @@ struct SizeLaunch {
         k_update_board<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, actions);
         return cudaGetLastError();
     }
+    static cudaError_t selfplay(const SelfPlayParams &p, cudaStream_t q) {
+        k_selfplay<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        return cudaGetLastError();
+    }
+    static cudaError_t selfplay_new_game(oth_state s, oth_selfplay sp, i64 B, u64 seed, i64 base, int init_rand,
+                                         u32 game_index, const int8_t *protagonist_in, cudaStream_t q) {
+        k_selfplay_new_game<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, sp, B, seed, base, init_rand, game_index, protagonist_in);
+        return cudaGetLastError();
+    }
     static const OthSizeOps *ops() {
-        static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board, &update_board};
+        static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board, &update_board,
+                                     &selfplay, &selfplay_new_game};
         return &o;
     }
 };

@@ -1,0 +1,255 @@
+"""Envs / PPOEnvs -- the PPO self-play vec-env of the reference, on the device.
+
+Mirrors the reference's ``envs.py`` (``Envs`` :7-41, ``PPOEnvs`` :188-257) and the worker
+side of the protocol (``subproc_worker`` / ``rule_base_game``,
+``ppo_run_self_play.py:244-441``).  The reference forks one process per env and moves
+every ply through pickled pipes; here B envs live on one B200 and a "round"
+(``PPOEnvs.step``) is: one ``oth_selfplay_begin`` launch, then per ``policy.act`` call one
+``oth_selfplay_advance`` launch (bookkeeping + rules step + next observation fused), then
+two ``oth_observe`` launches that expand the finished tuples.  What each env hands the
+learner per round is bit-identical to the reference worker's message (see
+tests/test_gpu_selfplay.py): the protagonist colour's (state, action, reward, done,
+choices, (value, log-prob, hidden)), reward = its own terminal reward or MINUS the reward
+of the opponent's reply, finished envs answering zeros / done / 'over'.
+
+Differences a caller sees (all tensors stay on the GPU):
+  * ``dones`` is a bool CUDA tensor [B] (reference: python list) -- use ``dones.all()``;
+  * ``infos`` is a ``SelfPlayInfos`` (``.type`` uint8 [B]: 0 = learning tuple, 1 = 'over';
+    ``.choices_mask`` bool [B, S*S]); ``infos[i]`` builds the reference's dict lazily;
+  * ``policy.act(obs, rnn_hxs, masks, choices)`` receives ``choices`` as the bool mask
+    [B, S*S] (``choices_as='lists'`` gives the reference's list of lists, with a sync);
+  * protagonist colours come from Philox (reference: the worker's global numpy RNG), or
+    from ``reset(protagonists=...)``.
+No CPU fallback: needs libothello_b200.so and a CUDA device.
+"""
+import ctypes as C
+
+import torch
+
+from . import _cabi
+from .vec_env import VecOthelloEnv
+
+
+class SelfPlayInfos(object):
+    """infos of one PPOEnvs.step: tensors + lazy reference-style dict access."""
+
+    def __init__(self, type_u8, choices_mask):
+        self.type = type_u8
+        self.choices_mask = choices_mask
+
+    def __len__(self):
+        return self.type.numel()
+
+    def __getitem__(self, i):
+        t = int(self.type[i].item())
+        return {"type": None if t == 0 else "over",
+                "choices": torch.nonzero(self.choices_mask[i]).flatten().tolist()}
+
+    def __iter__(self):
+        types = self.type.cpu().tolist()
+        masks = self.choices_mask.cpu()
+        for t, m in zip(types, masks):
+            yield {"type": None if t == 0 else "over", "choices": torch.nonzero(m).flatten().tolist()}
+
+    def choices(self):
+        """list of lists, like [info['choices'] for info in infos] (ppo_run_self_play.py:172)"""
+        return [d["choices"] for d in self]
+
+
+class Envs(object):
+    """envs.py:7-41.  `envs`: an int (number of lockstep envs) or, drop-in style, a list of
+    env objects whose first element supplies board_size / initial_rand_steps /
+    num_disk_as_reward / rand_seed / test_rand_steps_holder (ppo_run_self_play.py:99-109);
+    `subproc_worker` is accepted and ignored (there are no worker processes)."""
+
+    def __init__(self, envs, subproc_worker=None, policy=None, device=None, board_size=8, initial_rand_steps=0,
+                 num_disk_as_reward=True, seed=0, test_rand_steps=10, choices_as="mask", legacy_stale_state=True,
+                 env_id_base=0):
+        if isinstance(envs, int):
+            num = envs
+        else:
+            envs = list(envs)
+            num = len(envs)
+            e0 = envs[0]
+            board_size = getattr(e0, "board_size", board_size)
+            initial_rand_steps = getattr(e0, "initial_rand_steps", initial_rand_steps)
+            inner = getattr(e0, "env", e0)
+            num_disk_as_reward = getattr(inner, "num_disk_as_reward", num_disk_as_reward)
+            seed = getattr(e0, "rand_seed", seed)
+            test_rand_steps = getattr(e0, "test_rand_steps_holder", test_rand_steps)
+        if choices_as not in ("mask", "lists"):
+            raise ValueError("choices_as must be 'mask' or 'lists'")
+        self.num_processes = int(num)
+        self.policy = policy
+        self.choices_as = choices_as
+        self.test_rand_steps = int(test_rand_steps)
+        self.legacy_stale_state = bool(legacy_stale_state)
+        self.vec = VecOthelloEnv(self.num_processes, board_size=board_size, device=device, seed=seed,
+                                 initial_rand_steps=initial_rand_steps, sudden_death_on_invalid_move=True,
+                                 num_disk_as_reward=num_disk_as_reward, obs_layout="planes4",
+                                 obs_dtype=torch.float32, auto_reset=False, env_id_base=env_id_base)
+        self.device = self.vec.device
+        self._lib = self.vec._lib
+        S, N, B, W, dev = self.vec.board_size, self.vec.num_cells, self.num_processes, self.vec.words, self.device
+        self.board_size = S
+        self.observation_shape = (4, S, S)        # spaces.Box(zeros((4,S,S)), ones(...)), envs.py:16
+        self.num_actions = N                      # spaces.Discrete(S**2), envs.py:17
+        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)   # noqa: E731
+        self.protagonist = z((B,), torch.int8)
+        self._phase = z((B,), torch.uint8)
+        self._sav = {k: z((W, B), torch.int64) for k in ("black", "white", "legal", "choices")}
+        self._sav_meta = z((B,), torch.int32)
+        self._tr_action = z((B,), torch.int64)
+        self._tr_reward = z((B,), torch.float32)
+        self._tr_done = z((B,), torch.uint8)
+        self._tr_type = z((B,), torch.uint8)
+        self._tr_outputs = z((B, 3), torch.float32)
+        self._pend_outputs = z((B, 3), torch.float32)
+        self._pend_action = z((B,), torch.int64)
+        self._need = z((1,), torch.int32)
+        self._tr_obs = z((B, 4, S, S), torch.float32)
+        self._tr_choices_u8 = z((B, N), torch.uint8)
+        self._dummy_ctr = z((B,), torch.int32)
+        self._game_index = 0
+        self._c_sp = _cabi.OthSelfPlay(*[_cabi.ptr(t) for t in (
+            self.protagonist, self._phase, self._sav["black"], self._sav["white"], self._sav["legal"], self._sav_meta,
+            self._sav["choices"], self._tr_action, self._tr_reward, self._tr_done, self._tr_type, self._tr_outputs,
+            self._pend_outputs, self._pend_action)])
+        # the saved decision states seen as env states, for oth_observe
+        self._c_sav_state = _cabi.OthState(_cabi.ptr(self._sav["black"]), _cabi.ptr(self._sav["white"]),
+                                           _cabi.ptr(self._sav["legal"]), _cabi.ptr(self._sav_meta),
+                                           _cabi.ptr(self._dummy_ctr))
+        self._c_choice_state = _cabi.OthState(_cabi.ptr(self._sav["black"]), _cabi.ptr(self._sav["white"]),
+                                              _cabi.ptr(self._sav["choices"]), _cabi.ptr(self._sav_meta),
+                                              _cabi.ptr(self._dummy_ctr))
+        self._c_tr_obs_out = _cabi.OthOutputs(_cabi.ptr(self._tr_obs), None, None, None, None, None, None,
+                                              _cabi.OBS_PLANES4, _cabi.DTYPE_F32)
+        self._c_tr_choice_out = _cabi.OthOutputs(None, _cabi.ptr(self._tr_choices_u8), None, None, None, None, None,
+                                                 _cabi.OBS_NONE, _cabi.DTYPE_I8)
+        self.policy_calls = 0
+
+    # ------------------------------------------------------------------ envs.py:27-35
+    def over(self):
+        """envs.py:27-29 tells the workers to exit; nothing to tear down here."""
+
+    def reset(self, protagonists=None):
+        """envs.py:31-35 + the worker's 'reset' (ppo_run_self_play.py:261-270): new game in
+        every env, protagonist colour drawn per env (or given: int8/long tensor of -1/+1)."""
+        v = self.vec
+        pin = None
+        if protagonists is not None:
+            pin = torch.as_tensor(protagonists).to(device=self.device, dtype=torch.int8).reshape(-1).contiguous()
+            if pin.numel() != self.num_processes:
+                raise ValueError("protagonists must have one entry per env")
+        with v._on_device():
+            _cabi.check(self._lib.oth_selfplay_new_game(v._state(), self._c_sp, self.num_processes, v.board_size,
+                                                        v.seed_value, v.env_id_base, v.initial_rand_steps,
+                                                        self._game_index, _cabi.ptr(pin), v._stream()),
+                        "oth_selfplay_new_game")
+        self._game_index += 1
+
+    def step(self, *args):
+        raise NotImplementedError()
+
+    def test(self, *args):
+        raise NotImplementedError()
+
+    # ------------------------------------------------------------------ helpers
+    def _flags(self):
+        return self.vec._flags() | (0 if self.legacy_stale_state else _cabi.F_SP_FRESH_STATE)
+
+    def _choices_arg(self, mask):
+        if self.choices_as == "mask":
+            return mask
+        m = mask.cpu()
+        return [torch.nonzero(r).flatten().tolist() for r in m]
+
+    def _as_dev(self, x, dtype):
+        t = torch.as_tensor(x)
+        return t.to(device=self.device, dtype=dtype).reshape(-1).contiguous()
+
+
+class PPOEnvs(Envs):
+    """envs.py:188-257 (self-play)."""
+
+    def step(self, ex_hiddens):
+        v = self.vec
+        B = self.num_processes
+        flags = self._flags()
+        with v._on_device():
+            _cabi.check(self._lib.oth_selfplay_begin(v._state(), self._c_sp, B, v.board_size, flags,
+                                                     v._outputs(with_scalars=False), _cabi.ptr(self._need),
+                                                     v._stream()), "oth_selfplay_begin")
+            need = int(self._need.item())
+            while need > 0:                                              # envs.py:200
+                emitted = (self._phase & _cabi.SP_EMITTED) != 0
+                masks = torch.where(emitted, 1.0 - self._tr_done.float(), torch.ones((), device=self.device)).unsqueeze(1)
+                with torch.no_grad():
+                    value, actions, logp, hidden = self.policy.act(v.obs, ex_hiddens, masks,
+                                                                   self._choices_arg(v.legal_mask))   # envs.py:203
+                self.policy_calls += 1
+                a = self._as_dev(actions, torch.int64)
+                val, lp, hid = (self._as_dev(x, torch.float32) for x in (value, logp, hidden))
+                if a.numel() != B or val.numel() != B or lp.numel() != B or hid.numel() != B:
+                    raise ValueError("policy.act must return one value / action / log-prob / hidden per env")
+                _cabi.check(self._lib.oth_selfplay_advance(v._state(), self._c_sp, B, v.board_size, flags, _cabi.ptr(a),
+                                                           _cabi.ptr(val), _cabi.ptr(lp), _cabi.ptr(hid), v.seed_value,
+                                                           v.env_id_base, v.initial_rand_steps,
+                                                           v._outputs(with_scalars=False), _cabi.ptr(self._need),
+                                                           v._stream()), "oth_selfplay_advance")
+                need = int(self._need.item())
+            # expand the tuples: observation planes from the saved decision state, choices from its bitset
+            zf = (flags | _cabi.F_ZERO_IF_TERMINATED) & ~_cabi.F_AUTO_RESET
+            _cabi.check(self._lib.oth_observe(self._c_sav_state, B, v.board_size, zf, self._c_tr_obs_out, v._stream()),
+                        "oth_observe")
+            _cabi.check(self._lib.oth_observe(self._c_choice_state, B, v.board_size, zf, self._c_tr_choice_out,
+                                              v._stream()), "oth_observe")
+        dones = self._tr_done.view(torch.bool)
+        masks = (1.0 - self._tr_done.float()).unsqueeze(1)               # envs.py:198
+        bad_masks = torch.ones((B, 1), dtype=torch.float32, device=self.device)   # envs.py:199: never 'bad_transition'
+        infos = SelfPlayInfos(self._tr_type, self._tr_choices_u8.view(torch.bool))
+        return (self._tr_obs, self._tr_action.float().unsqueeze(1), self._tr_reward.unsqueeze(1), dones, infos,
+                self._tr_outputs, masks, bad_masks)
+
+    def test(self, name, num_games, ex_hiddens, protagonists=None):
+        """envs.py:229-257 + rule_base_game (ppo_run_self_play.py:371-441): the learner plays
+        `num_games // num_envs` games per env against 'rand' | 'greedy' with the test opening
+        budget; a win = final reward from the learner's side > 0.  -> (games, wins)."""
+        if name not in ("rand", "greedy"):
+            raise ValueError("test opponent must be 'rand' or 'greedy'")
+        v = self.vec
+        B, N = self.num_processes, v.num_cells
+        per = int(num_games) // B
+        wins = torch.zeros((B,), dtype=torch.int64, device=self.device)
+        ones = torch.ones((B, 1), dtype=torch.float32, device=self.device)
+        for g in range(per):
+            pin = None
+            if protagonists is not None:
+                pin = torch.as_tensor(protagonists[g]).to(device=self.device, dtype=torch.int8).reshape(-1)
+                pin = pin.expand(B).contiguous() if pin.numel() == 1 else pin.contiguous()
+            with v._on_device():
+                _cabi.check(self._lib.oth_selfplay_new_game(v._state(), self._c_sp, B, v.board_size, v.seed_value,
+                                                            v.env_id_base, self.test_rand_steps, self._game_index,
+                                                            _cabi.ptr(pin), v._stream()), "oth_selfplay_new_game")
+            self._game_index += 1
+            saved_rand = v.initial_rand_steps
+            v.initial_rand_steps = self.test_rand_steps                 # :372
+            try:
+                v.refresh_outputs()
+                P = self.protagonist.clone()
+                for ply in range(N - 4):                                 # every valid ply fills one cell
+                    turn = v.player_turn.clone()
+                    live = ~v.terminated()
+                    with torch.no_grad():
+                        _, actions, _, _ = self.policy.act(v.obs, ex_hiddens, ones, self._choices_arg(v.legal_mask))
+                    a = self._as_dev(actions, torch.int64)
+                    scripted = v.policy_actions(name)
+                    mine = turn == P
+                    v.step(torch.where(mine, a, scripted))
+                    sign = torch.where(mine, 1.0, -1.0)
+                    wins += (live & v.done & (v.reward * sign > 0)).to(torch.int64)   # :432-439
+                    if ply % 8 == 7 and bool(v.terminated().all().item()):
+                        break
+            finally:
+                v.initial_rand_steps = saved_rand                        # :440
+        return per * B, int(wins.sum().item())

@@ -1,0 +1,75 @@
+"""Legal-move-restricted action sampling on the device.
+
+Replaces the per-env Python loops of the reference learner's ``Policy.act`` /
+``Policy.evaluate_actions`` (``pytorch_a2c_ppo_acktr_gail/a2c_ppo_acktr/model.py:60-150,
+156-198``): ``FixedCategorical(logits=logits[i][choices[i]])`` -> sample / mode / log_probs,
+one env at a time on the host.  Here one kernel (``oth_masked_categorical``, a warp per
+env) reads the learner's logits [B, S*S] and the env's legal-move BITSET (no dense mask,
+no lists) and returns the action and its log-probability under softmax(logits[legal]).
+Edge cases follow the reference: no legal move -> action 0, log-prob 0 (:71-73); in
+evaluate mode an action that is not a legal choice gets log-prob 0 (:172-173).
+"""
+import ctypes as C
+
+import torch
+
+from . import _cabi
+
+_MODES = {"sample": _cabi.CAT_SAMPLE, "mode": _cabi.CAT_MODE, "evaluate": _cabi.CAT_EVALUATE}
+
+
+def masked_categorical(logits, legal_words, board_size, mode="sample", actions=None, seed=0, counter=0, env_id_base=0):
+    """logits: float32 CUDA [B, S*S]; legal_words: int64 CUDA [W, B] bitsets (VecOthelloEnv._legal layout:
+    bit a of word a//64 = action a).  -> (actions int64 [B], log_probs float32 [B])."""
+    if mode not in _MODES:
+        raise ValueError("mode must be sample | mode | evaluate")
+    if not (isinstance(logits, torch.Tensor) and logits.is_cuda):
+        raise _cabi.OthelloB200Error("masked_categorical needs CUDA tensors (no CPU path)")
+    lib = _cabi.load()
+    S = int(board_size)
+    B = logits.shape[0]
+    if logits.dim() != 2 or logits.shape[1] != S * S:
+        raise ValueError("logits must be [B, board_size**2]")
+    logits = logits.detach().to(torch.float32).contiguous()
+    legal_words = legal_words.contiguous()
+    if legal_words.dtype != torch.int64 or tuple(legal_words.shape) != (_cabi.words_per_board(S), B):
+        raise ValueError("legal_words must be int64 [W, B]")
+    a_in = None
+    if mode == "evaluate":
+        if actions is None:
+            raise ValueError("evaluate mode needs actions")
+        a_in = actions.to(device=logits.device, dtype=torch.int64).reshape(-1).contiguous()
+        if a_in.numel() != B:
+            raise ValueError("actions must have one entry per env")
+    out_a = torch.empty((B,), dtype=torch.int64, device=logits.device)
+    out_lp = torch.empty((B,), dtype=torch.float32, device=logits.device)
+    with torch.cuda.device(logits.device):
+        stream = C.c_void_p(torch.cuda.current_stream(logits.device).cuda_stream)
+        _cabi.check(lib.oth_masked_categorical(_cabi.ptr(logits), _cabi.ptr(legal_words), B, S, _MODES[mode],
+                                               _cabi.ptr(a_in), int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter),
+                                               int(env_id_base), _cabi.ptr(out_a), _cabi.ptr(out_lp), stream),
+                    "oth_masked_categorical")
+    return out_a, out_lp
+
+
+class LegalMoveSampler(object):
+    """Stateful convenience over masked_categorical for one VecOthelloEnv: every sample() call
+    uses the next Philox counter, so a rollout is reproducible from (seed, env ids)."""
+
+    def __init__(self, env, seed=None):
+        self.env = env
+        self.seed = env.seed_value if seed is None else int(seed)
+        self.counter = 0
+
+    def sample(self, logits):
+        a, lp = masked_categorical(logits, self.env._legal, self.env.board_size, "sample", seed=self.seed,
+                                   counter=self.counter, env_id_base=self.env.env_id_base)
+        self.counter += 1
+        return a, lp
+
+    def mode(self, logits):
+        return masked_categorical(logits, self.env._legal, self.env.board_size, "mode")
+
+    def log_probs(self, logits, actions, legal_words=None):
+        lw = self.env._legal if legal_words is None else legal_words
+        return masked_categorical(logits, lw, self.env.board_size, "evaluate", actions=actions)[1]

@@ -63,6 +63,10 @@ typedef struct oth_state {
 #define OTH_F_DISK_REWARD    0x02  /* num_disk_as_reward (othello.py:225,446-459) */
 #define OTH_F_AUTO_RESET     0x04  /* finished envs restart inside the same step call */
 #define OTH_F_LEGACY_SINGLE_MOVE_PLANE 0x08 /* util.py:55: make_state legal plane is empty when exactly one move */
+#define OTH_F_ZERO_IF_TERMINATED 0x10 /* oth_observe: envs whose meta has the terminated bit get an all-zero obs
+                                         (the worker's `o`, ppo_run_self_play.py:246,274); legal_mask unaffected */
+#define OTH_F_SP_FRESH_STATE 0x20     /* oth_selfplay_advance: refresh the saved state on EVERY protagonist ply
+                                         (default: keep ppo_run_self_play.py:291-301's stale state in pass runs) */
 
 /* observation layouts (plane count P, each plane S*S cells, env-major [B][P][S][S]) */
 #define OTH_OBS_NONE        0
@@ -169,6 +173,74 @@ int oth_set_board(oth_state st, int64_t B, int board_size, const int8_t *cells, 
  * actions[i] and turns the bracketed runs; no validity check (a cell without brackets just
  * receives the disc), turn / cached list / terminal flags untouched; out-of-range = no-op. */
 int oth_update_board(oth_state st, int64_t B, int board_size, const int64_t *actions, void *stream);
+
+/* ---------------------------------------------------------------------------------------
+ * PPO self-play protocol (envs.py:188-227 PPOEnvs.step + ppo_run_self_play.py:244-368
+ * subproc_worker), batched: every env plays BOTH colours with the same learner; the tuple
+ * handed to the learner per round is the protagonist colour's (state, action, reward, done,
+ * choices, (v, logp, hidden)) -- reward = its own terminal reward, or MINUS the reward of
+ * the opponent's reply (:306,345).  One "round" = one PPOEnvs.step call:
+ *   oth_selfplay_begin    clears the per-round flags; finished envs answer 'over' (:273-274)
+ *   loop while *need_count > 0:  policy net on (obs, legal_mask) -> actions, v, logp, hidden
+ *       oth_selfplay_advance     applies them to the envs that still owe a tuple
+ *   oth_observe on {sav_black, sav_white, sav_legal, sav_meta} with OTH_F_ZERO_IF_TERMINATED
+ *       gives the tuple's observation planes; sav_choices is its `choices` list as a bitset.
+ */
+typedef struct oth_selfplay {
+    int8_t   *protagonist;  /* [B] colour the learner is credited for in this game: -1 BLACK / +1 WHITE (:265-267) */
+    uint8_t  *phase;        /* [B] OTH_SP_* bits */
+    uint64_t *sav_black;    /* [W][B] state_b / state_w of the pending decision (:283,323,360) */
+    uint64_t *sav_white;    /* [W][B] */
+    uint64_t *sav_legal;    /* [W][B] its possible_moves at that time (plane 3 of make_state) */
+    uint32_t *sav_meta;     /* [B] bit0 turn plane; bit1 set = the tuple's observation is all zeros */
+    uint64_t *sav_choices;  /* [W][B] info['choices'] of the tuple (:286-287 choice_b / choice_w) */
+    int64_t  *tr_action;    /* [B] action_b / action_w (the learner's choice, even when the opening override replaced it) */
+    float    *tr_reward;    /* [B] */
+    uint8_t  *tr_done;      /* [B] */
+    uint8_t  *tr_type;      /* [B] 0 = learning tuple (info['type'] None), 1 = 'over' */
+    float    *tr_outputs;   /* [B][3] value, log-prob, hidden of the decision (output_b / output_w) */
+    float    *pend_outputs; /* [B][3] same, for the decision still waiting for its reward */
+    int64_t  *pend_action;  /* [B] */
+} oth_selfplay;
+
+#define OTH_SP_PENDING  0x01  /* a protagonist decision waits for its reward */
+#define OTH_SP_EMITTED  0x02  /* this env has produced its tuple for the current round */
+#define OTH_SP_FINISHED 0x04  /* game over: answers 'over' until the next oth_selfplay_new_game */
+#define OTH_SP_PREV_P   0x08  /* the previous ply of this game was the protagonist's (pass run) */
+
+/* `cmd == 'reset'` of the worker (:261-270) for every env: oth_reset + phase cleared + protagonist colour drawn
+ * from Philox stream 2 (counter = game_index) unless protagonist_in (device, [B], -1/+1) is given. */
+int oth_selfplay_new_game(oth_state st, oth_selfplay sp, int64_t B, int board_size, uint64_t seed, int64_t env_id_base,
+                          int init_rand_steps, uint64_t game_index, const int8_t *protagonist_in, void *stream);
+
+/* Start of a round: clears OTH_SP_EMITTED, emits the 'over' tuple of finished envs, writes out.obs / out.legal_mask /
+ * out.player_turn for the CURRENT state (the first `need_action` message, :285) and sets *need_count (device int32)
+ * to the number of envs that still owe a tuple. */
+int oth_selfplay_begin(oth_state st, oth_selfplay sp, int64_t B, int board_size, int flags, oth_outputs out,
+                       int32_t *need_count, void *stream);
+
+/* One `policy.act` worth of progress (envs.py:200-217): every env that still owes a tuple applies actions[i]
+ * (subject to the random-opening override, othello.py:70-73), with value[i] / logp[i] / hidden[i] recorded when
+ * the mover is the protagonist.  Envs whose tuple is now complete get OTH_SP_EMITTED and their tr_* / sav_* rows
+ * filled; the others stay in `need_action`.  out.* is rewritten for the new current state; *need_count is set to
+ * the number of envs still owing a tuple. */
+int oth_selfplay_advance(oth_state st, oth_selfplay sp, int64_t B, int board_size, int flags, const int64_t *actions,
+                         const float *value, const float *logp, const float *hidden, uint64_t seed,
+                         int64_t env_id_base, int init_rand_steps, oth_outputs out, int32_t *need_count, void *stream);
+
+/* Legal-move-restricted categorical over the learner's logits (model.py:60-150 Policy.act, :156-198
+ * evaluate_actions): the distribution is softmax(logits[i][choices_i]), choices_i = set bits of legal[.][i].
+ *   mode OTH_CAT_SAMPLE    action ~ that distribution (inverse CDF in ascending action order, one Philox draw,
+ *                          stream 3, counter = `counter`); logp_out = its log-probability
+ *   mode OTH_CAT_MODE      action = first argmax (deterministic=True)
+ *   mode OTH_CAT_EVALUATE  logp_out = log-probability of actions_in[i]; 0 when it is not a legal choice (:172-173)
+ * No legal move: action 0, logp 0 (:71-73).  float32 arithmetic, max-subtracted log-sum-exp. */
+#define OTH_CAT_SAMPLE   0
+#define OTH_CAT_MODE     1
+#define OTH_CAT_EVALUATE 2
+int oth_masked_categorical(const float *logits, const uint64_t *legal, int64_t B, int board_size, int mode,
+                           const int64_t *actions_in, uint64_t seed, uint64_t counter, int64_t env_id_base,
+                           int64_t *actions_out, float *logp_out, void *stream);
 
 /* Measurement helper: a dependency-limited LOP3/SHF/IADD3 stream on every SM; writes
  * the number of thread-level integer instructions executed to *instr_out_host after the
