@@ -356,10 +356,38 @@ OTH_DEV Philox4 philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, u32 k0, u32 k1) {
     o.v[0] = c0; o.v[1] = c1; o.v[2] = c2; o.v[3] = c3;
     return o;
 }
+// The ten round keys depend on the seed only: the hot kernel takes them precomputed by the
+// host as launch parameters, so every round's key is a constant-bank operand of the XOR
+// instead of two per-thread IADDs (20 ALU-pipe instructions per draw).
+struct PhiloxKeys { u32 k0[10], k1[10]; };
+__host__ __device__ inline PhiloxKeys philox_round_keys(u64 seed) {
+    PhiloxKeys K;
+    u32 a = (u32)seed, b = (u32)(seed >> 32);
+    for (int r = 0; r < 10; r++) { K.k0[r] = a; K.k1[r] = b; a += 0x9E3779B9u; b += 0xBB67AE85u; }
+    return K;
+}
+OTH_DEV Philox4 philox4x32_10(u32 c0, u32 c1, u32 c2, u32 c3, const PhiloxKeys &K) {
+    const u32 M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        u32 hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        u32 hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        u32 n0 = hi1 ^ c1 ^ K.k0[r], n2 = hi0 ^ c3 ^ K.k1[r];
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    }
+    Philox4 o;
+    o.v[0] = c0; o.v[1] = c1; o.v[2] = c2; o.v[3] = c3;
+    return o;
+}
 #define OTH_STREAM_ENV 0u      // opening budget, opening moves, fused random policy
 #define OTH_STREAM_POLICY 1u   // oth_policy(random)
 OTH_DEV u32 philox_draw(u64 seed, i64 gid, u32 stream, u32 ctr) {
     Philox4 b = philox4x32_10(ctr >> 2, stream, (u32)(u64)gid, (u32)((u64)gid >> 32), (u32)seed, (u32)(seed >> 32));
+    u32 k = ctr & 3u;
+    return k == 0 ? b.v[0] : (k == 1 ? b.v[1] : (k == 2 ? b.v[2] : b.v[3]));
+}
+OTH_DEV u32 philox_draw(const PhiloxKeys &K, i64 gid, u32 stream, u32 ctr) {
+    Philox4 b = philox4x32_10(ctr >> 2, stream, (u32)(u64)gid, (u32)((u64)gid >> 32), K);
     u32 k = ctr & 3u;
     return k == 0 ? b.v[0] : (k == 1 ? b.v[1] : (k == 2 ? b.v[2] : b.v[3]));
 }
@@ -381,8 +409,8 @@ OTH_DEV int meta_winner(u32 m) { int c = (m >> OTH_META_WINNER_SHIFT) & 3; retur
 OTH_DEV u32 winner_code(int w) { return w > 0 ? 1u : (w < 0 ? 2u : 0u); }
 
 // OthelloBaseEnv.reset (othello.py:265-271) + opening budget (othello.py:62-64)
-template <int S>
-OTH_DEV void env_reset(EnvRegs<S> &e, u64 seed, i64 gid, int init_rand_steps) {
+template <int S, class KEY>
+OTH_DEV void env_reset(EnvRegs<S> &e, const KEY &seed, i64 gid, int init_rand_steps) {
     e.black = geo_start_black<S>();
     e.white = geo_start_white<S>();
     e.legal = geo_start_legal<S>();

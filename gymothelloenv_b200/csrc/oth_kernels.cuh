@@ -52,6 +52,14 @@ OTH_DEV void plane_rows(int p, bool turn_white, bool quirk_empty, bool zero, int
 // 4 bits -> 4 bytes of 0/1 (bit i of n lands on bit 8*i: n*0x00204081 places it at
 // i, i+7, i+14, i+21 without carries; the mask keeps position 8*i)
 OTH_DEV u32 spread4(u32 n) { return (n * 0x00204081u) & 0x01010101u; }
+// one staged nibble -> register (zero-extended byte load).  Spelled as PTX so that nvcc cannot
+// merge four neighbouring byte loads into one LDS.32 + four PRMT extractions: the extraction
+// would sit on the ALU pipe (the binding unit of k_step), the byte loads sit on the idle LSU.
+OTH_DEV u32 lds_u8(u32 saddr) {
+    u32 v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+    return v;
+}
 OTH_DEV u32 cells4_i8(u32 pn, u32 nn) { return spread4(nn) * 0xFFu + spread4(pn); }   // +1 / -1 bytes
 OTH_DEV u32 cell_f32(u32 pbit, u32 nbit) { return (pbit ? 0x3F800000u : 0u) | (nbit ? 0xBF800000u : 0u); }
 
@@ -159,8 +167,8 @@ OTH_DEV void fast8_full(void *base, i64 env0, const WarpStage<8> &st, int lane) 
     constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
     const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
     if constexpr (ES == 1) {
-        const unsigned char *src = rows + ROW0 * 512 + lane * 4;
-        const unsigned char *nsrc = rows + NIB_NEG0 * 512 + lane * 4;
+        const u32 src = (u32)__cvta_generic_to_shared(rows) + ROW0 * 512 + lane * 4;
+        const u32 nsrc = (u32)__cvta_generic_to_shared(rows) + NIB_NEG0 * 512 + lane * 4;
         char *dst = reinterpret_cast<char *>(base) + env0 * (i64)(P * 64) + (lane >> 2) * (P * 64) + (lane & 3) * 16;
 #pragma unroll
         for (int p = 0; p < P; p++) {
@@ -169,8 +177,8 @@ OTH_DEV void fast8_full(void *base, i64 env0, const WarpStage<8> &st, int lane) 
                 u32 w[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    w[j] = spread4(src[p * 512 + k * 128 + j]);
-                    if (HAS_NEG && p == 0) w[j] = spread4(nsrc[k * 128 + j]) * 0xFFu + w[j];
+                    w[j] = spread4(lds_u8(src + p * 512 + k * 128 + j));
+                    if (HAS_NEG && p == 0) w[j] = spread4(lds_u8(nsrc + k * 128 + j)) * 0xFFu + w[j];
                 }
                 *reinterpret_cast<uint4 *>(dst + k * (8 * P * 64) + p * 64) = make_uint4(w[0], w[1], w[2], w[3]);
             }
@@ -416,6 +424,7 @@ struct StepParams {
     i64 base;
     int init_rand;
     oth_outputs out;
+    PhiloxKeys keys;     // philox_round_keys(seed), filled by the launcher
 };
 
 template <int S>
@@ -435,7 +444,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
             i64 action = -1;
             const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
             if (opening || p.action_source == OTH_ACT_RANDOM) {
-                action = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                action = random_pick<S>(e.legal, philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
                 e.ctr++;
                 if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
             } else if (p.action_source == OTH_ACT_GREEDY) {
@@ -445,7 +454,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
                 action = p.actions[i];
             }
             r = env_step<S>(e, action, p.flags);
-            if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+            if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.keys, p.base + i, p.init_rand);
             store_env<S>(e, p.st, i, p.B);
         }
         if (p.out.reward) p.out.reward[i] = (float)r.reward;
@@ -766,7 +775,9 @@ struct SizeLaunch {
         k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
         return cudaGetLastError();
     }
-    static cudaError_t step(const StepParams &p, cudaStream_t q) {
+    static cudaError_t step(const StepParams &p0, cudaStream_t q) {
+        StepParams p = p0;
+        p.keys = philox_round_keys(p.seed);
         k_step<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
         return cudaGetLastError();
     }
