@@ -180,14 +180,16 @@ OTH_DEV BB<Geo<S>::W> dir_moves(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &p
     return sh<STEP, LEFT, W>(run);
 }
 
-// ---- 8x8 legal moves ---------------------------------------------------------------
+// ---- single-word boards (S <= 8): legal moves -----------------------------------------
 // East: adding the cells just east of own discs to the inner-column opponent mask makes
 // the carry ripple through each bracket-able run and land on the cell behind it (edge
-// columns are 0 in the mask, so a carry never leaves its row).  West = the same on
-// bit-reversed boards (BREV runs off the ALU pipe).  The three other axes use paired
-// fills that share the doubled propagator between the two opposite directions.
+// columns are 0 in the mask and a row is S contiguous bits, so a carry never leaves its
+// row).  West = the same on bit-reversed boards (BREV runs off the ALU pipe; the reversed
+// board sits in the top S*S bits, rows still contiguous).  The three other axes use paired
+// Kogge-Stone fills (steps 1, 2, 2 cover the longest run, S-2 <= 6) that share the doubled
+// propagator between the two opposite directions.
 template <int D>
-OTH_DEV u64 pair_moves8(u64 P, u64 m) {
+OTH_DEV u64 pair_moves1(u64 P, u64 m) {
     u64 fl = m & (P << D), fr = m & (P >> D);
     fl |= m & (fl << D);
     fr |= m & (fr >> D);
@@ -198,15 +200,18 @@ OTH_DEV u64 pair_moves8(u64 P, u64 m) {
     fr |= pr & (fr >> (2 * D));
     return (fl << D) | (fr >> D);
 }
-OTH_DEV u64 legal8(u64 P, u64 O) {
-    const u64 Oi = O & 0x7E7E7E7E7E7E7E7Eull;
+template <int S>
+OTH_DEV u64 legal1(u64 P, u64 O) {
+    static_assert(Geo<S>::W == 1, "single-word boards only");
+    const u64 Oi = O & GeoWord<S, 0>::inner;
     u64 moves = (Oi + ((P << 1) & Oi)) & ~Oi;
     const u64 Pr = __brevll(P), Or = __brevll(Oi);
     moves |= __brevll((Or + ((Pr << 1) & Or)) & ~Or);
-    moves |= pair_moves8<8>(P, O);
-    moves |= pair_moves8<7>(P, Oi);
-    moves |= pair_moves8<9>(P, Oi);
-    return moves & ~(P | O);
+    moves |= pair_moves1<S>(P, O);
+    moves |= pair_moves1<S - 1>(P, Oi);
+    moves |= pair_moves1<S + 1>(P, Oi);
+    if constexpr (S == 8) return moves & ~(P | O);
+    else return moves & ~(P | O) & GeoWord<S, 0>::full;
 }
 
 // othello.py:313-343: empty cells from which >=1 direction holds a run of opponent discs
@@ -214,9 +219,9 @@ OTH_DEV u64 legal8(u64 P, u64 O) {
 template <int S>
 OTH_DEV BB<Geo<S>::W> legal(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
     constexpr int W = Geo<S>::W;
-    if constexpr (S == 8) {
+    if constexpr (W == 1) {
         BB<W> r;
-        r.w[0] = legal8(own.w[0], opp.w[0]);
+        r.w[0] = legal1<S>(own.w[0], opp.w[0]);
         return r;
     }
     const BB<W> inner = opp & geo_inner<S>();
@@ -239,7 +244,7 @@ OTH_DEV BB<Geo<S>::W> dir_flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &ow
     return bb_select(any(closed), flood & pro, bb_zero<W>());
 }
 
-// ---- 8x8 flips by carry propagation -------------------------------------------------
+// ---- single-word boards (S <= 8): flips by carry propagation ---------------------------
 // For a ray of cells above the move (towards higher bit indices) with mask m:
 //   x = O | ~m ; t = x + 1 : the +1 carry ripples through every non-ray bit and through the
 //   contiguous opponent discs at the start of the ray and stops on the first ray cell that
@@ -247,26 +252,41 @@ OTH_DEV BB<Geo<S>::W> dir_flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &ow
 //   is bracketed: flipped = (stop - 1) & m.
 // The four rays towards lower indices are the same computation on bit-reversed boards.
 // Rays are mv * pattern (mv is a power of two, so the 64-bit IMADs are shifts that run on
-// the FMA pipe instead of the saturated ALU pipe).  Masking the opponent with the inner
-// columns for the horizontal / diagonal rays stops a run at the board edge (no wrap).
-OTH_DEV u64 ray_flips8(u64 m, u64 P, u64 O) {
+// the FMA pipe instead of the saturated ALU pipe); ray cells past the last board bit hold
+// neither colour, so they can only end a run unbracketed.  Masking the opponent with the
+// inner columns for the horizontal / diagonal rays stops a run at the board edge (no wrap).
+constexpr u64 geo_ray_pattern(int S, int D) {
+    u64 m = 0;
+    for (int k = 1; k < S; k++)
+        if (k * D < 64) m |= 1ull << (k * D);
+    return m;
+}
+template <int S>
+struct GeoRays {
+    static constexpr u64 e = geo_ray_pattern(S, 1), s = geo_ray_pattern(S, S);
+    static constexpr u64 se = geo_ray_pattern(S, S + 1), sw = geo_ray_pattern(S, S - 1);
+};
+OTH_DEV u64 ray_flips1(u64 m, u64 P, u64 O) {
     const u64 x = O | ~m;
     const u64 t = x + 1ull;
     const u64 stop = t & ~x & P;                       // 0 or the single closing own disc
     const u64 d = stop - (stop != 0ull ? 1ull : 0ull); // bits below the closing disc
     return d & m;
 }
-OTH_DEV u64 flips8_up(u64 mv, u64 P, u64 O) {
-    const u64 Oi = O & 0x7E7E7E7E7E7E7E7Eull;
-    u64 f = ray_flips8(mv * 0x00000000000000FEull, P, Oi);          // +1
-    f |= ray_flips8(mv * 0x0101010101010100ull, P, O);             // +8
-    f |= ray_flips8(mv * 0x8040201008040200ull, P, Oi);            // +9
-    f |= ray_flips8(mv * 0x0002040810204080ull, P, Oi);            // +7
+template <int S>
+OTH_DEV u64 flips1_up(u64 mv, u64 P, u64 O, u64 Oi) {
+    u64 f = ray_flips1(mv * GeoRays<S>::e, P, Oi);
+    f |= ray_flips1(mv * GeoRays<S>::s, P, O);
+    f |= ray_flips1(mv * GeoRays<S>::se, P, Oi);
+    f |= ray_flips1(mv * GeoRays<S>::sw, P, Oi);
     return f;
 }
-OTH_DEV u64 flips8(u64 mv, u64 P, u64 O) {
-    const u64 up = flips8_up(mv, P, O);
-    const u64 dn = flips8_up(__brevll(mv), __brevll(P), __brevll(O));
+template <int S>
+OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
+    static_assert(Geo<S>::W == 1, "single-word boards only");
+    const u64 Oi = O & GeoWord<S, 0>::inner;
+    const u64 up = flips1_up<S>(mv, P, O, Oi);
+    const u64 dn = flips1_up<S>(__brevll(mv), __brevll(P), __brevll(O), __brevll(Oi));
     return up | __brevll(dn);
 }
 
@@ -275,9 +295,9 @@ OTH_DEV u64 flips8(u64 mv, u64 P, u64 O) {
 template <int S>
 OTH_DEV BB<Geo<S>::W> flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
     constexpr int W = Geo<S>::W;
-    if constexpr (S == 8) {
+    if constexpr (W == 1) {
         BB<W> f;
-        f.w[0] = flips8(mv.w[0], own.w[0], opp.w[0]);
+        f.w[0] = flips1<S>(mv.w[0], own.w[0], opp.w[0]);
         return f;
     } else {
         const BB<W> inner = opp & geo_inner<S>();

@@ -16,10 +16,19 @@ constexpr int OTH_WARPS = OTH_BLOCK / 32;
 enum { ROW_BLACK = 0, ROW_WHITE = 1, ROW_LEGAL = 2, ROW_ZERO = 3, ROW_ONES = 4, ROW_COUNT = 5 };
 #define OTH_LAYOUT_MASK_INTERNAL 6   // the dense legal_mask buffer, written with the same machinery
 
-template <int S>
-struct WarpStage {
+// Even board sizes (S*S % 4 == 0) stage NIBBLES (see "nibble staging" below); odd sizes stage
+// the raw bitboards and pay per-cell index arithmetic in warp_write_planes.
+enum { NIB_POS0 = 0, NIB_POS1 = 1, NIB_POS2 = 2, NIB_POS3 = 3, NIB_NEG0 = 4, NIB_MASK = 5, NIB_ROWS = 6 };
+template <int S, bool NIB = ((S * S) % 4 == 0)>
+struct WarpStageT {
     u64 row[ROW_COUNT][Geo<S>::W][32];
 };
+template <int S>
+struct WarpStageT<S, true> {
+    uint4 nib[NIB_ROWS][32][Geo<S>::W];     // [row][env lane][16 nibbles per 64 cells, one per byte]
+};
+template <int S>
+using WarpStage = WarpStageT<S>;
 
 __host__ __device__ constexpr int layout_planes(int layout) {
     return layout == OTH_OBS_BOARD_MASK ? 2 : (layout == OTH_OBS_PLANES4 ? 4 : (layout == OTH_OBS_PLANES3 ? 3 : 1));
@@ -137,11 +146,6 @@ OTH_DEV void warp_write_layout(int layout, void *base, i64 env0, int nenv, const
 // ALU pipe -- the binding unit of k_step, see profiles/ -- does ~1 op per 4 cells
 // instead of ~9, and the address of the 4 nibbles of int8 chunk c is simply 4*c.
 // ---------------------------------------------------------------------------------
-enum { NIB_POS0 = 0, NIB_POS1 = 1, NIB_POS2 = 2, NIB_POS3 = 3, NIB_NEG0 = 4, NIB_MASK = 5, NIB_ROWS = 6 };
-template <>
-struct WarpStage<8> {
-    uint4 nib[NIB_ROWS][32];
-};
 
 OTH_DEV uint4 nibble_bytes(u64 x) {
     const u32 lo = (u32)x, hi = (u32)(x >> 32);
@@ -165,7 +169,7 @@ OTH_DEV void fast8_full(void *base, i64 env0, const WarpStage<8> &st, int lane) 
     constexpr int P = layout_planes(LAYOUT);
     constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
     constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
-    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
+    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0][0]);
     if constexpr (ES == 1) {
         const u32 src = (u32)__cvta_generic_to_shared(rows) + ROW0 * 512 + lane * 4;
         const u32 nsrc = (u32)__cvta_generic_to_shared(rows) + NIB_NEG0 * 512 + lane * 4;
@@ -212,7 +216,7 @@ __device__ __noinline__ void fast8_write(void *base, i64 env0, int nenv, const W
     constexpr int P = layout_planes(LAYOUT);
     constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
     constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
-    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0]);
+    const unsigned char *rows = reinterpret_cast<const unsigned char *>(&st.nib[0][0][0]);
     char *slab = reinterpret_cast<char *>(base) + env0 * (i64)(P * 64 * ES);
     if (nenv == 32) {
         fast8_full<LAYOUT, ES>(base, env0, st, lane);
@@ -272,45 +276,126 @@ OTH_DEV void fast8_write_layout(int layout, void *base, i64 env0, int nenv, cons
     }
 }
 
-OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, bool zero_mask, int flags,
-                              const oth_outputs &out, i64 warp_env0, i64 B, WarpStage<8> &st) {
+// Any even board size: group g (4 cells = one staged nibble) of the warp's output slab belongs to
+// (env, plane) q = g / (N/4) and is nibble r = g % (N/4) of that plane; a 16-byte int8 chunk is four
+// consecutive groups (it may straddle a plane or env boundary when N/4 is not a multiple of 4), a
+// 16-byte float32 chunk is one group.  One division by a constant per chunk, then increments.
+template <int S, int LAYOUT, int ES>
+__device__ __noinline__ void nib_write(void *base, i64 env0, int nenv, const WarpStage<S> &st, int lane) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, P = layout_planes(LAYOUT);
+    constexpr int G4 = N / 4, RB = 16 * W;
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    constexpr int ROW0 = (LAYOUT == OTH_LAYOUT_MASK_INTERNAL) ? NIB_MASK : NIB_POS0;
+    const u32 rows = (u32)__cvta_generic_to_shared(&st.nib[0][0][0]);
+    char *slab = reinterpret_cast<char *>(base) + env0 * (i64)(P * N * ES);
+    const int ngroups = nenv * P * G4;
+    if constexpr (ES == 1) {
+        const int nchunks = (ngroups + 3) >> 2;
+        for (int c = lane; c < nchunks; c += 32) {
+            int q = (4 * c) / G4;
+            int r = 4 * c - q * G4;
+            int e = q / P, p = q - e * P;
+            u32 w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int ec = min(e, 31);                                  // ragged tail of the last warp
+                w[j] = spread4(lds_u8(rows + ((ROW0 + p) * 32 + ec) * RB + r));
+                if (HAS_NEG && p == 0) w[j] = spread4(lds_u8(rows + (NIB_NEG0 * 32 + ec) * RB + r)) * 0xFFu + w[j];
+                if (++r == G4) { r = 0; if (++p == P) { p = 0; e++; } }
+            }
+            char *dst = slab + (i64)c * 16;
+            if (4 * c + 4 <= ngroups) {
+                *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+            } else {
+                for (int j = 0; 4 * c + j < ngroups; j++) *reinterpret_cast<u32 *>(dst + 4 * j) = w[j];
+            }
+        }
+    } else {
+        for (int c = lane; c < ngroups; c += 32) {
+            const int q = c / G4, r = c - q * G4;
+            const int e = q / P, p = q - e * P;
+            const u32 n = lds_u8(rows + ((ROW0 + p) * 32 + e) * RB + r);
+            u32 w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) w[j] = (n & (1u << j)) * (0x3F800000u >> j);
+            if (HAS_NEG && p == 0) {
+                const u32 nn = lds_u8(rows + (NIB_NEG0 * 32 + e) * RB + r);
+#pragma unroll
+                for (int j = 0; j < 4; j++) w[j] |= (nn & (1u << j)) * (0xBF800000u >> j);
+            }
+            *reinterpret_cast<uint4 *>(slab + (i64)c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+    }
+}
+
+template <int S, int ES>
+OTH_DEV void nib_write_layout(int layout, void *base, i64 env0, int nenv, const WarpStage<S> &st, int lane) {
+    if constexpr (S == 8) {
+        fast8_write_layout<ES>(layout, base, env0, nenv, st, lane);
+    } else {
+        switch (layout) {
+        case OTH_OBS_BOARD: nib_write<S, OTH_OBS_BOARD, ES>(base, env0, nenv, st, lane); break;
+        case OTH_OBS_BOARD_MASK: nib_write<S, OTH_OBS_BOARD_MASK, ES>(base, env0, nenv, st, lane); break;
+        case OTH_OBS_PLANES4: nib_write<S, OTH_OBS_PLANES4, ES>(base, env0, nenv, st, lane); break;
+        case OTH_OBS_PLANES3: nib_write<S, OTH_OBS_PLANES3, ES>(base, env0, nenv, st, lane); break;
+        case OTH_OBS_ABSOLUTE: nib_write<S, OTH_OBS_ABSOLUTE, ES>(base, env0, nenv, st, lane); break;
+        default: break;
+        }
+    }
+}
+
+template <int W>
+OTH_DEV void stage_nibbles(uint4 *dst, const BB<W> &x) {
+    BB_FOR(k) dst[k] = nibble_bytes(x.w[k]);
+}
+
+// even S: stage this lane's env as nibbles and write every requested dense output for the warp
+template <int S>
+OTH_DEV void emit_dense_nib(const EnvRegs<S> &e, bool active, bool zero_obs, bool zero_mask, int flags,
+                            const oth_outputs &out, i64 warp_env0, i64 B, WarpStage<S> &st) {
+    constexpr int W = Geo<S>::W;
     const int lane = threadIdx.x & 31;
     const bool live = active && !zero_obs;
     const bool tw = e.meta & OTH_META_TURN_WHITE;
-    const u64 black = live ? e.black.w[0] : 0ull, white = live ? e.white.w[0] : 0ull, lg = live ? e.legal.w[0] : 0ull;
-    const u64 lg_mask = (active && !zero_mask) ? e.legal.w[0] : 0ull;
+    const BB<W> zero = bb_zero<W>();
+    const BB<W> black = bb_select(live, e.black, zero), white = bb_select(live, e.white, zero);
+    const BB<W> lg = bb_select(live, e.legal, zero);
+    const BB<W> lg_mask = bb_select(active && !zero_mask, e.legal, zero);
     const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
     if (layout == OTH_OBS_BOARD || layout == OTH_OBS_BOARD_MASK) {           // othello.py:363-376
-        st.nib[NIB_POS0][lane] = nibble_bytes(tw ? white : black);
-        st.nib[NIB_NEG0][lane] = nibble_bytes(tw ? black : white);
-        if (layout == OTH_OBS_BOARD_MASK) st.nib[NIB_POS1][lane] = nibble_bytes(lg);
+        stage_nibbles<W>(st.nib[NIB_POS0][lane], bb_select(tw, white, black));
+        stage_nibbles<W>(st.nib[NIB_NEG0][lane], bb_select(tw, black, white));
+        if (layout == OTH_OBS_BOARD_MASK) stage_nibbles<W>(st.nib[NIB_POS1][lane], lg);
     } else if (layout == OTH_OBS_ABSOLUTE) {
-        st.nib[NIB_POS0][lane] = nibble_bytes(white);
-        st.nib[NIB_NEG0][lane] = nibble_bytes(black);
+        stage_nibbles<W>(st.nib[NIB_POS0][lane], white);
+        stage_nibbles<W>(st.nib[NIB_NEG0][lane], black);
     } else if (layout == OTH_OBS_PLANES4 || layout == OTH_OBS_PLANES3) {     // util.py:48-74
-        st.nib[NIB_POS0][lane] = nibble_bytes(black);
-        st.nib[NIB_POS1][lane] = nibble_bytes(white);
+        stage_nibbles<W>(st.nib[NIB_POS0][lane], black);
+        stage_nibbles<W>(st.nib[NIB_POS1][lane], white);
         const u32 t = (live && tw) ? 0x0F0F0F0Fu : 0u;
-        st.nib[NIB_POS2][lane] = make_uint4(t, t, t, t);
+        BB_FOR(k) st.nib[NIB_POS2][lane][k] = make_uint4(t, t, t, t);
         if (layout == OTH_OBS_PLANES4) {
-            const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && __popcll(lg) <= 1;   // util.py:55
-            st.nib[NIB_POS3][lane] = quirk ? z : nibble_bytes(lg);
+            const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(lg) <= 1;   // util.py:55
+            stage_nibbles<W>(st.nib[NIB_POS3][lane], bb_select(quirk, zero, lg));
         }
     }
-    if (out.legal_mask != nullptr) st.nib[NIB_MASK][lane] = nibble_bytes(lg_mask);
+    if (out.legal_mask != nullptr) stage_nibbles<W>(st.nib[NIB_MASK][lane], lg_mask);
     __syncwarp();
     if (warp_env0 < B) {
         const int nenv = (int)min((i64)32, B - warp_env0);
-        if (layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8 && nenv == 32) {
-            fast8_full<OTH_OBS_BOARD, 1>(out.obs, warp_env0, st, lane);          // the headline path, inlined
+        if (S == 8 && layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8 && nenv == 32) {
+            if constexpr (S == 8) fast8_full<OTH_OBS_BOARD, 1>(out.obs, warp_env0, st, lane);   // the headline path, inlined
         } else if (layout != OTH_OBS_NONE) {
-            if (out.obs_dtype == OTH_DTYPE_F32) fast8_write_layout<4>(layout, out.obs, warp_env0, nenv, st, lane);
-            else fast8_write_layout<1>(layout, out.obs, warp_env0, nenv, st, lane);
+            if (out.obs_dtype == OTH_DTYPE_F32) nib_write_layout<S, 4>(layout, out.obs, warp_env0, nenv, st, lane);
+            else nib_write_layout<S, 1>(layout, out.obs, warp_env0, nenv, st, lane);
         }
         if (out.legal_mask != nullptr) {
-            if (nenv == 32) fast8_full<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, st, lane);
-            else fast8_write<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+            if constexpr (S == 8) {
+                if (nenv == 32) fast8_full<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, st, lane);
+                else fast8_write<OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+            } else {
+                nib_write<S, OTH_LAYOUT_MASK_INTERNAL, 1>(out.legal_mask, warp_env0, nenv, st, lane);
+            }
         }
     }
     __syncwarp();
@@ -320,8 +405,8 @@ OTH_DEV void emit_dense_fast8(const EnvRegs<8> &e, bool active, bool zero_obs, b
 template <int S>
 OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, bool zero_mask, int flags,
                         const oth_outputs &out, i64 warp_env0, i64 B, WarpStage<S> &st) {
-    if constexpr (S == 8) {
-        emit_dense_fast8(e, active, zero_obs, zero_mask, flags, out, warp_env0, B, st);
+    if constexpr ((S * S) % 4 == 0) {
+        emit_dense_nib<S>(e, active, zero_obs, zero_mask, flags, out, warp_env0, B, st);
     } else {
         constexpr int W = Geo<S>::W;
         const int lane = threadIdx.x & 31;
