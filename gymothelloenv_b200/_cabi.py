@@ -42,6 +42,7 @@ EXPORTED_SYMBOLS = (
     "oth_abi_version", "oth_last_error", "oth_words_per_board", "oth_reset", "oth_observe", "oth_step",
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
     "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
+    "oth_epsilon_greedy",
 )
 
 
@@ -122,6 +123,9 @@ def load():
     L.oth_masked_categorical.restype = C.c_int
     L.oth_masked_categorical.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
                                          C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oth_epsilon_greedy.restype = C.c_int
+    L.oth_epsilon_greedy.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
+                                     C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     if L.oth_abi_version() != 1:
         raise OthelloB200Error("libothello_b200.so ABI version mismatch")
     _lib = L

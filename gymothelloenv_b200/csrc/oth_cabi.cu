@@ -330,6 +330,99 @@ OTH_API int oth_masked_categorical(const float *logits, const uint64_t *legal, i
     return cuda_result(cudaGetLastError(), "oth_masked_categorical");
 }
 
+// ---- epsilon-greedy over the legal moves (dqn.py:264-275,478-488) --------------------
+// One warp per env, lane l holds q of actions l, l+32, ...  Explore: the n-th set bit of the
+// legal bitset (= the n-th entry of the ascending possible_moves list).  Exploit: first argmax.
+#define OTH_STREAM_EPSILON 4u
+__global__ void __launch_bounds__(128) k_epsilon_greedy(const float *q, const u64 *legal, i64 B, int N, float epsilon,
+                                                        u64 seed, u64 counter, i64 base, i64 *actions_out,
+                                                        float *q_chosen_out, uint8_t *explored_out) {
+    const i64 env = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= B) return;
+    const int K = (N + 31) >> 5, W = (N + 63) >> 6;
+    const float NEG_INF = __int_as_float(0xFF800000u);
+    u64 words[3] = {0ull, 0ull, 0ull};
+    int n_legal = 0;
+#pragma unroll
+    for (int w = 0; w < 3; w++)
+        if (w < W) { words[w] = legal[(i64)w * B + env]; n_legal += __popcll(words[w]); }
+    float x[CAT_MAXK];
+    float best = NEG_INF;
+    int bi = 0x7FFFFFFF;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const int a = 32 * k + lane;
+        x[k] = 0.f;
+        if (k < K && a < N) {
+            const u64 word = (a >> 6) == 0 ? words[0] : ((a >> 6) == 1 ? words[1] : words[2]);
+            const bool ok = (word >> (a & 63)) & 1ull;
+            if (ok) {
+                x[k] = q[env * N + a];
+                // strict > over ascending actions inside the lane; NaN never wins, as in a max-scan
+                if (bi == 0x7FFFFFFF || x[k] > best) { best = x[k]; bi = a; }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+        const int oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+        if (oi != 0x7FFFFFFF && (bi == 0x7FFFFFFF || ob > best || (ob == best && oi < bi))) { best = ob; bi = oi; }
+    }
+    int chosen = 0;
+    bool explored = false;
+    if (n_legal > 0) {
+        const u32 ctr0 = (u32)(2ull * counter), hi = (u32)((2ull * counter) >> 32);
+        const u32 r0 = philox_draw(seed, base + env, OTH_STREAM_EPSILON + 16u * hi, ctr0);
+        const float u = (float)(r0 >> 8) * (1.0f / 16777216.0f);
+        explored = epsilon >= u;                                   // dqn.py:266
+        if (explored) {
+            const u32 r1 = philox_draw(seed, base + env, OTH_STREAM_EPSILON + 16u * hi, ctr0 + 1u);
+            int n = bounded(r1, n_legal);                          // random.randrange(len(possible_moves))
+            int wsel = 0;
+#pragma unroll
+            for (int w = 0; w < 2; w++) {
+                const int c = __popcll(words[w]);
+                if (wsel == w && n >= c) { n -= c; wsel = w + 1; }
+            }
+            const u64 word = wsel == 0 ? words[0] : (wsel == 1 ? words[1] : words[2]);
+            chosen = 64 * wsel + nth_bit64(word, n);
+        } else {
+            chosen = bi;
+        }
+    }
+    float qc = 0.f;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const float v = __shfl_sync(0xFFFFFFFFu, x[k], chosen & 31);
+        if ((chosen >> 5) == k) qc = v;
+    }
+    if (lane == 0) {
+        if (actions_out) actions_out[env] = (i64)chosen;
+        if (q_chosen_out) q_chosen_out[env] = n_legal > 0 ? qc : 0.f;
+        if (explored_out) explored_out[env] = explored ? 1 : 0;
+    }
+}
+
+OTH_API int oth_epsilon_greedy(const float *q, const uint64_t *legal, int64_t B, int board_size, float epsilon,
+                               uint64_t seed, uint64_t counter, int64_t env_id_base, int64_t *actions_out,
+                               float *q_chosen_out, uint8_t *explored_out, void *stream) {
+    const OthSizeOps *ops = ops_for(board_size);
+    if (ops == nullptr) return fail(OTH_ERR_BAD_BOARD_SIZE, "board_size unsupported");
+    if (B < 0) return fail(OTH_ERR_BAD_ARG, "negative count");
+    if (q == nullptr || legal == nullptr) return fail(OTH_ERR_NULL_POINTER, "q / legal is null");
+    if (actions_out == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions_out is null");
+    if (!(epsilon >= 0.f && epsilon <= 1.f)) return fail(OTH_ERR_BAD_ARG, "epsilon must be in [0, 1]");
+    if (board_size * board_size > 32 * CAT_MAXK) return fail(OTH_ERR_BAD_BOARD_SIZE, "board too large for the sampler");
+    if (B == 0) return 0;
+    const unsigned grid = (unsigned)((B * 32 + 127) / 128);
+    k_epsilon_greedy<<<grid, 128, 0, (cudaStream_t)stream>>>(q, (const u64 *)legal, B, board_size * board_size, epsilon,
+                                                             seed, counter, env_id_base, (i64 *)actions_out,
+                                                             q_chosen_out, explored_out);
+    return cuda_result(cudaGetLastError(), "oth_epsilon_greedy");
+}
+
 // ---- INT32 ALU probe: 8 independent LOP3/SHF/IADD3 chains per thread -----------------
 #define PROBE_UNROLL 16
 __global__ void k_int_alu_probe(uint32_t *sink, int iters) {

@@ -73,3 +73,77 @@ class LegalMoveSampler(object):
     def log_probs(self, logits, actions, legal_words=None):
         lw = self.env._legal if legal_words is None else legal_words
         return masked_categorical(logits, lw, self.env.board_size, "evaluate", actions=actions)[1]
+
+
+def epsilon_greedy(q_values, legal_words, board_size, epsilon, seed=0, counter=0, env_id_base=0):
+    """The DQN agent's action choice (reference ``dqn.py:264-275`` / ``:478-488``) for a whole batch: with
+    probability ``epsilon`` a uniformly random legal move, else the legal move with the largest q (first
+    occurrence on ties).  q_values: float32 CUDA [B, S*S]; legal_words: int64 CUDA [W, B].
+    -> (actions int64 [B], q_chosen float32 [B], explored bool [B])."""
+    if not (isinstance(q_values, torch.Tensor) and q_values.is_cuda):
+        raise _cabi.OthelloB200Error("epsilon_greedy needs CUDA tensors (no CPU path)")
+    lib = _cabi.load()
+    S = int(board_size)
+    B = q_values.shape[0]
+    if q_values.dim() != 2 or q_values.shape[1] != S * S:
+        raise ValueError("q_values must be [B, board_size**2]")
+    if not 0.0 <= float(epsilon) <= 1.0:
+        raise ValueError("epsilon must be in [0, 1]")
+    q_values = q_values.detach().to(torch.float32).contiguous()
+    legal_words = legal_words.contiguous()
+    if legal_words.dtype != torch.int64 or tuple(legal_words.shape) != (_cabi.words_per_board(S), B):
+        raise ValueError("legal_words must be int64 [W, B]")
+    out_a = torch.empty((B,), dtype=torch.int64, device=q_values.device)
+    out_q = torch.empty((B,), dtype=torch.float32, device=q_values.device)
+    out_e = torch.empty((B,), dtype=torch.uint8, device=q_values.device)
+    with torch.cuda.device(q_values.device):
+        stream = C.c_void_p(torch.cuda.current_stream(q_values.device).cuda_stream)
+        _cabi.check(lib.oth_epsilon_greedy(_cabi.ptr(q_values), _cabi.ptr(legal_words), B, S, float(epsilon),
+                                           int(seed) & 0xFFFFFFFFFFFFFFFF, int(counter), int(env_id_base),
+                                           _cabi.ptr(out_a), _cabi.ptr(out_q), _cabi.ptr(out_e), stream),
+                    "oth_epsilon_greedy")
+    return out_a, out_q, out_e.bool()
+
+
+class EpsilonGreedy(object):
+    """The exploration schedule of the reference DQN agent (``dqn.py:144-146,175,196-201,264-286,403``) over
+    one VecOthelloEnv: epsilon starts at ``initial_epsilon``; while ``t < initial_replay_size`` every action is
+    random (``:266``); afterwards epsilon drops by ``(initial - final) / anealing_steps`` per get_action call
+    until it reaches ``final_epsilon`` (``:283-284``).  The guard is the reference's ``epsilon > final_epsilon``
+    on the accumulated float, so epsilon can end one decrement BELOW ``final_epsilon`` (1.0 -> 0.1 over 10 steps
+    settles at 0.01); that is kept, not clamped.  ``t`` counts agent steps (``:403``): one per lockstep
+    call here, as the reference counts one per env step of its single env."""
+
+    def __init__(self, env, anealing_steps=1000000, initial_epsilon=1.0, final_epsilon=0.1,
+                 initial_replay_size=20000, test_epsilon=0.05, seed=None):
+        self.env = env
+        self.epsilon = float(initial_epsilon)
+        self.final_epsilon = float(final_epsilon)
+        self.anealing_by_step = (float(initial_epsilon) - float(final_epsilon)) / anealing_steps
+        self.initial_replay_size = int(initial_replay_size)
+        self.test_epsilon = float(test_epsilon)
+        self.seed = env.seed_value if seed is None else int(seed)
+        self.t = 0
+        self.counter = 0
+
+    def _choose(self, q_values, eps):
+        out = epsilon_greedy(q_values, self.env._legal, self.env.board_size, eps, seed=self.seed,
+                             counter=self.counter, env_id_base=self.env.env_id_base)
+        self.counter += 1
+        return out
+
+    def get_action(self, q_values):
+        """dqn.py:264-286.  -> (actions, q_chosen, explored); call ``tick()`` once per stored transition."""
+        eps = 1.0 if self.t < self.initial_replay_size else min(1.0, max(0.0, self.epsilon))
+        out = self._choose(q_values, eps)
+        if self.epsilon > self.final_epsilon and self.t >= self.initial_replay_size:
+            self.epsilon -= self.anealing_by_step
+        return out
+
+    def get_action_at_test(self, q_values):
+        """dqn.py:478-488: epsilon fixed at 0.05."""
+        return self._choose(q_values, self.test_epsilon)
+
+    def tick(self, n=1):
+        """dqn.py:403 ``self.t += 1`` (the reference advances t in ``run``, once per transition)."""
+        self.t += int(n)

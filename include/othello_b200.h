@@ -242,6 +242,19 @@ int oth_masked_categorical(const float *logits, const uint64_t *legal, int64_t B
                            const int64_t *actions_in, uint64_t seed, uint64_t counter, int64_t env_id_base,
                            int64_t *actions_out, float *logp_out, void *stream);
 
+/* Epsilon-greedy over the legal moves, the DQN agent's action choice (dqn.py:264-275 get_action,
+ * :478-488 get_action_at_test): with probability epsilon (`epsilon >= u`, u uniform in [0,1) as at dqn.py:266)
+ * a uniformly random entry of the ascending legal list, else the legal move with the largest q value, FIRST
+ * occurrence on ties (torch.argmax over q[0][possible_moves], :271-273).  q is float32 [B, S*S]; legal as above.
+ * Randomness: Philox stream 4 of env (env_id_base + i); word 2*counter decides explore / exploit
+ * (u = (word >> 8) * 2^-24), word 2*counter+1 picks the random entry (multiply-shift).  The reference draws
+ * from Python's `random`, so only the DISTRIBUTION can match it, not the stream (stated in DESIGN.md).
+ * q_chosen_out[i] = q[i][action] (may be null); explored_out[i] = 1 when the random branch was taken (may be
+ * null).  No legal move: action 0, q_chosen 0, explored 0 (the reference never asks in that state). */
+int oth_epsilon_greedy(const float *q, const uint64_t *legal, int64_t B, int board_size, float epsilon,
+                       uint64_t seed, uint64_t counter, int64_t env_id_base, int64_t *actions_out,
+                       float *q_chosen_out, uint8_t *explored_out, void *stream);
+
 /* Measurement helper: a dependency-limited LOP3/SHF/IADD3 stream on every SM; writes
  * the number of thread-level integer instructions executed to *instr_out_host after the
  * launch is enqueued (the count is static). Used by bench.py to measure the INT32-ALU
