@@ -31,8 +31,9 @@ def decide(h, choices_i):
 
 
 class FakePolicy(object):
-    def __init__(self, board_size):
+    def __init__(self, board_size, salt=0):
         self.board_size = int(board_size)
+        self.salt = int(salt)             # teacher / student stand-ins differ by salt (0 = the self-play golden)
         self.calls = 0
 
     def act(self, obs, rnn_hxs, masks, choices, deterministic=False):
@@ -42,7 +43,7 @@ class FakePolicy(object):
             m = choices.detach().cpu().numpy() if hasattr(choices, "detach") else np.asarray(choices)
             choices = [np.nonzero(row)[0].tolist() for row in m]
         self.calls += 1
-        hs = obs_hash(obs, self.board_size)
+        hs = (obs_hash(obs, self.board_size) + self.salt) % _MOD
         B = len(hs)
         act = np.zeros((B, 1), dtype=np.int64)
         v = np.zeros((B,), dtype=np.float32)
