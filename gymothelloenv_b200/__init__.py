@@ -8,11 +8,11 @@ kernels behind a C ABI (``include/othello_b200.h``).  No CPU fallback.
 from . import _cabi
 from ._cabi import OthelloB200Error
 from .vec_env import VecOthelloEnv, shard_range
-from .envs import Envs, PPOEnvs
+from .envs import Envs, PPOEnvs, PPOTeacherStudentEnvs
 from .sampling import masked_categorical, LegalMoveSampler, epsilon_greedy, EpsilonGreedy
 
 BLACK_DISK = -1   # othello.py:10
 NO_DISK = 0       # othello.py:11
 WHITE_DISK = 1    # othello.py:12
 
-__all__ = ["VecOthelloEnv", "Envs", "PPOEnvs", "masked_categorical", "LegalMoveSampler", "epsilon_greedy", "EpsilonGreedy", "OthelloB200Error", "shard_range", "BLACK_DISK", "NO_DISK", "WHITE_DISK"]
+__all__ = ["VecOthelloEnv", "Envs", "PPOEnvs", "PPOTeacherStudentEnvs", "masked_categorical", "LegalMoveSampler", "epsilon_greedy", "EpsilonGreedy", "OthelloB200Error", "shard_range", "BLACK_DISK", "NO_DISK", "WHITE_DISK"]

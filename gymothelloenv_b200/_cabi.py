@@ -23,6 +23,10 @@ F_SP_FRESH_STATE = 0x20
 
 # self-play phase bits (OTH_SP_*) and categorical modes (OTH_CAT_*)
 SP_PENDING, SP_EMITTED, SP_FINISHED, SP_PREV_P = 0x01, 0x02, 0x04, 0x08
+# teacher/student phase bits and tuple types (OTH_TS_*)
+TS_EMITTED, TS_FINISHED, TS_PEND_BLACK, TS_PEND_WHITE = 0x01, 0x02, 0x04, 0x08
+TS_PREV_BLACK, TS_PREV_WHITE, TS_QUEUED, TS_QUEUED_WHITE = 0x10, 0x20, 0x40, 0x80
+TS_TYPE_BLACK, TS_TYPE_WHITE, TS_TYPE_OVER = 0, 1, 2
 CAT_SAMPLE, CAT_MODE, CAT_EVALUATE = 0, 1, 2
 
 OBS_NONE, OBS_BOARD, OBS_BOARD_MASK, OBS_PLANES4, OBS_PLANES3, OBS_ABSOLUTE = 0, 1, 2, 3, 4, 5
@@ -42,7 +46,7 @@ EXPORTED_SYMBOLS = (
     "oth_abi_version", "oth_last_error", "oth_words_per_board", "oth_reset", "oth_observe", "oth_step",
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
     "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
-    "oth_epsilon_greedy",
+    "oth_epsilon_greedy", "oth_ts_new_game", "oth_ts_begin", "oth_ts_advance",
 )
 
 
@@ -61,6 +65,13 @@ class OthSelfPlay(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
         "protagonist", "phase", "sav_black", "sav_white", "sav_legal", "sav_meta", "sav_choices", "tr_action",
         "tr_reward", "tr_done", "tr_type", "tr_outputs", "pend_outputs", "pend_action")]
+
+
+class OthTeacherStudent(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "phase", "sav_black", "sav_white", "sav_legal", "sav_meta", "sav_choices", "sav_action", "sav_outputs",
+        "queued_reward", "tr_black", "tr_white", "tr_legal", "tr_choices", "tr_meta", "tr_action", "tr_reward",
+        "tr_done", "tr_type", "tr_who", "tr_outputs")]
 
 
 class OthPolicySpec(C.Structure):
@@ -126,6 +137,16 @@ def load():
     L.oth_epsilon_greedy.restype = C.c_int
     L.oth_epsilon_greedy.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                      C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oth_ts_new_game.restype = C.c_int
+    L.oth_ts_new_game.argtypes = [OthState, OthTeacherStudent, C.c_int64, C.c_int, C.c_uint64, C.c_int64, C.c_int,
+                                  C.c_void_p]
+    L.oth_ts_begin.restype = C.c_int
+    L.oth_ts_begin.argtypes = [OthState, OthTeacherStudent, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, OthOutputs,
+                               C.c_void_p, C.c_void_p]
+    L.oth_ts_advance.restype = C.c_int
+    L.oth_ts_advance.argtypes = [OthState, OthTeacherStudent, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
+                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int64, C.c_int,
+                                 OthOutputs, C.c_void_p, C.c_void_p]
     if L.oth_abi_version() != 1:
         raise OthelloB200Error("libothello_b200.so ABI version mismatch")
     _lib = L

@@ -215,6 +215,69 @@ OTH_API int oth_selfplay_advance(oth_state st, oth_selfplay sp, int64_t B, int b
     return selfplay_launch(ops, p, stream, "oth_selfplay_advance");
 }
 
+// ---- teacher / student protocol (envs.py:44-140, ppo_run_teacher_vs_student.py:425-560) ----
+static int check_ts(const oth_teacher_student &t) {
+    if (!t.phase || !t.sav_black || !t.sav_white || !t.sav_legal || !t.sav_meta || !t.sav_choices || !t.sav_action ||
+        !t.sav_outputs || !t.queued_reward || !t.tr_black || !t.tr_white || !t.tr_legal || !t.tr_choices || !t.tr_meta ||
+        !t.tr_action || !t.tr_reward || !t.tr_done || !t.tr_type || !t.tr_who || !t.tr_outputs)
+        return fail(OTH_ERR_NULL_POINTER, "null teacher/student pointer");
+    return 0;
+}
+
+OTH_API int oth_ts_new_game(oth_state st, oth_teacher_student ts, int64_t B, int board_size, uint64_t seed,
+                            int64_t env_id_base, int init_rand_steps, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_ts(ts)) return rc;
+    if (init_rand_steps < 0 || init_rand_steps > 254) return fail(OTH_ERR_BAD_ARG, "init_rand_steps must be in 0..254");
+    if (B == 0) return 0;
+    return cuda_result(ops->ts_new_game(st, ts, B, seed, env_id_base, init_rand_steps, (cudaStream_t)stream),
+                       "oth_ts_new_game");
+}
+
+static int ts_launch(const OthSizeOps *ops, TeacherStudentParams &p, void *stream, const char *what) {
+    if (p.need_count == nullptr) return fail(OTH_ERR_NULL_POINTER, "need_count is null");
+    if (p.teacher != 1 && p.teacher != -1) return fail(OTH_ERR_BAD_ARG, "teacher must be -1 or +1");
+    cudaError_t e = cudaMemsetAsync(p.need_count, 0, 2 * sizeof(int), (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_result(e, what);
+    return cuda_result(ops->teacher_student(p, (cudaStream_t)stream), what);
+}
+
+OTH_API int oth_ts_begin(oth_state st, oth_teacher_student ts, int64_t B, int board_size, int flags, int teacher,
+                         float teacher_done_reward, oth_outputs out, int32_t *need_count, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_ts(ts)) return rc;
+    if (int rc = check_outputs(out)) return rc;
+    if (B == 0) return 0;
+    TeacherStudentParams p;
+    memset(&p, 0, sizeof(p));
+    p.st = st; p.ts = ts; p.B = B; p.flags = flags; p.mode = 0; p.teacher = teacher;
+    p.teacher_done_reward = teacher_done_reward; p.out = out; p.need_count = need_count;
+    return ts_launch(ops, p, stream, "oth_ts_begin");
+}
+
+OTH_API int oth_ts_advance(oth_state st, oth_teacher_student ts, int64_t B, int board_size, int flags, int teacher,
+                           float teacher_done_reward, int colour, const int64_t *actions, const float *value,
+                           const float *logp, const float *hidden, uint64_t seed, int64_t env_id_base,
+                           int init_rand_steps, oth_outputs out, int32_t *need_count, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (int rc = check_ts(ts)) return rc;
+    if (int rc = check_outputs(out)) return rc;
+    if (actions == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions is null");
+    if (colour != 1 && colour != -1) return fail(OTH_ERR_BAD_ARG, "colour must be -1 or +1");
+    if (init_rand_steps < 0 || init_rand_steps > 254) return fail(OTH_ERR_BAD_ARG, "init_rand_steps must be in 0..254");
+    if (B == 0) return 0;
+    TeacherStudentParams p;
+    memset(&p, 0, sizeof(p));
+    p.st = st; p.ts = ts; p.B = B; p.flags = flags; p.mode = 1; p.teacher = teacher;
+    p.teacher_done_reward = teacher_done_reward; p.colour = colour; p.actions = (const i64 *)actions;
+    p.value = value; p.logp = logp; p.hidden = hidden; p.seed = seed; p.base = env_id_base;
+    p.init_rand = init_rand_steps; p.out = out; p.need_count = need_count;
+    return ts_launch(ops, p, stream, "oth_ts_advance");
+}
+
 // ---- legal-move-restricted categorical (model.py:60-150,156-198) ---------------------
 // One warp per env; lane l holds actions l, l+32, ... (N <= 160).  float32, max-subtracted.
 #define OTH_STREAM_SAMPLE 3u

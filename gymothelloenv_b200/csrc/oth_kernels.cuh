@@ -681,6 +681,161 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_selfplay_new_game(oth_state s, ot
         : (int8_t)((philox_draw(seed, base + i, OTH_STREAM_PROTAGONIST, game_index) & 1u) ? 1 : -1);   // :265-266
 }
 
+// -------------------------------------------------------------------- teacher / student
+// The per-env machine behind PPOTeacherStudentEnvs.step + othello_teacher_vs_student (envs.py:63-140,
+// ppo_run_teacher_vs_student.py:425-560), see include/othello_b200.h.  mode 0 = start of a call,
+// mode 1 = one policy[colour].act worth of plies.
+struct TeacherStudentParams {
+    oth_state st;
+    oth_teacher_student ts;
+    i64 B;
+    int flags;
+    int mode;
+    int teacher;                 // -1 | +1
+    float teacher_done_reward;   // sum_k(win_avg[k] - last_win_avg[k])   (:460-461)
+    int colour;                  // mode 1: the colour being served
+    const i64 *actions;
+    const float *value, *logp, *hidden;
+    u64 seed;
+    i64 base;
+    int init_rand;
+    oth_outputs out;
+    int *need_count;             // [2]: envs waiting for a black / a white action
+};
+
+// copies colour c's saved decision into the tr_* row of env i (:457-470 send_transition)
+template <int S>
+OTH_DEV void ts_emit(const TeacherStudentParams &p, i64 i, int c, int raw_reward, bool done) {
+    constexpr int W = Geo<S>::W;
+    const oth_teacher_student &t = p.ts;
+    const i64 B = p.B;
+    BB_FOR(k) {
+        const i64 s = ((i64)c * W + k) * B + i;
+        t.tr_black[k * B + i] = t.sav_black[s];
+        t.tr_white[k * B + i] = t.sav_white[s];
+        t.tr_legal[k * B + i] = t.sav_legal[s];
+        t.tr_choices[k * B + i] = t.sav_choices[s];
+    }
+    t.tr_meta[i] = t.sav_meta[(i64)c * B + i];
+    t.tr_action[i] = t.sav_action[(i64)c * B + i];
+    const int colour = c == 0 ? -1 : 1;
+    const bool is_teacher = colour == p.teacher;
+    t.tr_reward[i] = is_teacher ? (done ? p.teacher_done_reward : 0.f) : (float)raw_reward;
+    t.tr_done[i] = done ? 1 : 0;
+    t.tr_type[i] = (uint8_t)(c == 0 ? OTH_TS_TYPE_BLACK : OTH_TS_TYPE_WHITE);
+    t.tr_who[i] = is_teacher ? 0 : 1;
+#pragma unroll
+    for (int j = 0; j < 3; j++) t.tr_outputs[3 * i + j] = t.sav_outputs[3 * ((i64)c * B + i) + j];
+}
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_teacher_student(TeacherStudentParams p) {
+    constexpr int W = Geo<S>::W;
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    const bool active = i < p.B;
+    const oth_teacher_student &t = p.ts;
+    EnvRegs<S> e = empty_env<S>();
+    bool need_b = false, need_w = false;
+    if (active) {
+        load_env<S>(e, p.st, i, p.B);
+        u32 ph = t.phase[i];
+        if (p.mode == 0) {
+            ph &= ~(u32)OTH_TS_EMITTED;
+            if (ph & OTH_TS_FINISHED) {
+                if (ph & OTH_TS_QUEUED) {                          // the last mover's own tuple (:505-509 / :546-551)
+                    ts_emit<S>(p, i, (ph & OTH_TS_QUEUED_WHITE) ? 1 : 0, t.queued_reward[i], true);
+                    ph &= ~(u32)(OTH_TS_QUEUED | OTH_TS_QUEUED_WHITE);
+                } else {                                           // 'over' (:470-471); envs.py:124-130 counts it as white
+                    BB_FOR(k) { t.tr_choices[k * p.B + i] = 0ull; }
+                    t.tr_meta[i] = OTH_META_TERMINATED;
+                    t.tr_action[i] = 0; t.tr_reward[i] = 0.f; t.tr_done[i] = 1;
+                    t.tr_type[i] = OTH_TS_TYPE_OVER;
+                    t.tr_who[i] = p.teacher == 1 ? 0 : 1;
+                    t.tr_outputs[3 * i] = 0.f; t.tr_outputs[3 * i + 1] = 0.f; t.tr_outputs[3 * i + 2] = 0.f;
+                }
+                ph |= OTH_TS_EMITTED;
+            }
+        } else if (!(ph & OTH_TS_EMITTED)) {
+            const bool wm = e.meta & OTH_META_TURN_WHITE;
+            const int mover = wm ? 1 : -1;
+            if (mover == p.colour) {
+                const int c = wm ? 1 : 0, o = 1 - c;
+                const u32 prev_c = wm ? OTH_TS_PREV_WHITE : OTH_TS_PREV_BLACK;
+                const u32 pend_c = wm ? OTH_TS_PEND_WHITE : OTH_TS_PEND_BLACK;
+                const u32 pend_o = wm ? OTH_TS_PEND_BLACK : OTH_TS_PEND_WHITE;
+                const i64 a_pol = p.actions[i];
+                // c's decision: state at the start of c's run, the rest refreshed every ply
+                if (!(ph & prev_c) || (p.flags & OTH_F_SP_FRESH_STATE)) {
+                    BB_FOR(k) {
+                        const i64 s = ((i64)c * W + k) * p.B + i;
+                        t.sav_black[s] = e.black.w[k]; t.sav_white[s] = e.white.w[k]; t.sav_legal[s] = e.legal.w[k];
+                    }
+                    t.sav_meta[(i64)c * p.B + i] = wm ? OTH_META_TURN_WHITE : 0u;
+                }
+                BB_FOR(k) { t.sav_choices[((i64)c * W + k) * p.B + i] = e.legal.w[k]; }
+                t.sav_action[(i64)c * p.B + i] = a_pol;
+                const i64 so = 3 * ((i64)c * p.B + i);
+                t.sav_outputs[so] = p.value ? p.value[i] : 0.f;
+                t.sav_outputs[so + 1] = p.logp ? p.logp[i] : 0.f;
+                t.sav_outputs[so + 2] = p.hidden ? p.hidden[i] : 0.f;
+                ph |= pend_c;
+                i64 action = a_pol;
+                if (meta_rand_cnt(e.meta) < meta_rand_max(e.meta)) {   // opening override (othello.py:70-73)
+                    action = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                    e.ctr++;
+                    e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+                }
+                const StepResult r = env_step<S>(e, action, p.flags);
+                const bool still_c = ((e.meta & OTH_META_TURN_WHITE) != 0) == wm;
+                if (!r.done && still_c) {                          // the other side passes (:486-488 / :529-531)
+                    ts_emit<S>(p, i, c, r.reward, false);
+                    ph |= OTH_TS_EMITTED;
+                } else if (ph & pend_o) {                          // :498-503 / :541-545
+                    ts_emit<S>(p, i, o, -r.reward, r.done != 0);
+                    ph |= OTH_TS_EMITTED;
+                    if (r.done) {
+                        t.queued_reward[i] = r.reward;
+                        ph |= OTH_TS_QUEUED | (wm ? OTH_TS_QUEUED_WHITE : 0u);
+                    }
+                } else if (r.done) {                               // :505-509 while `init` is still True
+                    ts_emit<S>(p, i, c, r.reward, true);
+                    ph |= OTH_TS_EMITTED;
+                }
+                ph = (ph & ~(u32)(OTH_TS_PREV_BLACK | OTH_TS_PREV_WHITE)) | prev_c;
+                if (r.done) ph |= OTH_TS_FINISHED;
+                store_env<S>(e, p.st, i, p.B);
+            }
+        }
+        t.phase[i] = (uint8_t)ph;
+        const bool need = !(ph & OTH_TS_EMITTED);
+        need_w = need && (e.meta & OTH_META_TURN_WHITE);
+        need_b = need && !(e.meta & OTH_META_TURN_WHITE);
+        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
+        if (p.out.done) p.out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
+    }
+    const u32 nb = __ballot_sync(0xFFFFFFFFu, need_b), nw = __ballot_sync(0xFFFFFFFFu, need_w);
+    if ((threadIdx.x & 31) == 0 && p.need_count != nullptr) {
+        if (nb != 0u) atomicAdd(&p.need_count[0], __popc(nb));
+        if (nw != 0u) atomicAdd(&p.need_count[1], __popc(nw));
+    }
+    const bool fin = active && (e.meta & OTH_META_TERMINATED);
+    emit_dense<S>(e, active, fin, fin, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+}
+
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_ts_new_game(oth_state s, oth_teacher_student ts, i64 B, u64 seed, i64 base,
+                                                           int init_rand) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    if (i >= B) return;
+    EnvRegs<S> e;
+    e.ctr = s.ctr[i];
+    env_reset<S>(e, seed, base + i, init_rand);
+    store_env<S>(e, s, i, B);
+    ts.phase[i] = 0;
+    ts.queued_reward[i] = 0;
+}
+
 // --------------------------------------------------------------------------- policy
 template <int S>
 __global__ void __launch_bounds__(OTH_BLOCK) k_policy(oth_state s, i64 B, int kind, int depth, u64 seed, u64 counter,
@@ -845,6 +1000,8 @@ struct OthSizeOps {
     cudaError_t (*update_board)(oth_state, i64, const i64 *, cudaStream_t);
     cudaError_t (*selfplay)(const SelfPlayParams &, cudaStream_t);
     cudaError_t (*selfplay_new_game)(oth_state, oth_selfplay, i64, u64, i64, int, u32, const int8_t *, cudaStream_t);
+    cudaError_t (*teacher_student)(const TeacherStudentParams &, cudaStream_t);
+    cudaError_t (*ts_new_game)(oth_state, oth_teacher_student, i64, u64, i64, int, cudaStream_t);
 };
 
 static inline unsigned oth_grid(i64 B) { return (unsigned)((B + OTH_BLOCK - 1) / OTH_BLOCK); }
@@ -893,9 +1050,18 @@ struct SizeLaunch {
         k_selfplay_new_game<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, sp, B, seed, base, init_rand, game_index, protagonist_in);
         return cudaGetLastError();
     }
+    static cudaError_t teacher_student(const TeacherStudentParams &p, cudaStream_t q) {
+        k_teacher_student<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        return cudaGetLastError();
+    }
+    static cudaError_t ts_new_game(oth_state s, oth_teacher_student ts, i64 B, u64 seed, i64 base, int init_rand,
+                                   cudaStream_t q) {
+        k_ts_new_game<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, ts, B, seed, base, init_rand);
+        return cudaGetLastError();
+    }
     static const OthSizeOps *ops() {
         static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board, &update_board,
-                                     &selfplay, &selfplay_new_game};
+                                     &selfplay, &selfplay_new_game, &teacher_student, &ts_new_game};
         return &o;
     }
 };

@@ -56,7 +56,52 @@ class SelfPlayInfos(object):
         return [d["choices"] for d in self]
 
 
-class Envs(object):
+class _RuleBaseGames(object):
+    """rule_base_game (ppo_run_self_play.py:371-441 == ppo_run_teacher_vs_student.py:575-645, identical text)
+    for all envs in lockstep; mixed into Envs."""
+
+    def _rule_base_games(self, policy, name, num_games, ex_hiddens, protagonists=None):
+        if name not in ("rand", "greedy"):
+            raise ValueError("test opponent must be 'rand' or 'greedy'")
+        v = self.vec
+        B, N = self.num_processes, v.num_cells
+        per = int(num_games) // B
+        wins = torch.zeros((B,), dtype=torch.int64, device=self.device)
+        ones = torch.ones((B, 1), dtype=torch.float32, device=self.device)
+        for g in range(per):
+            pin = None
+            if protagonists is not None:
+                pin = torch.as_tensor(protagonists[g]).to(device=self.device, dtype=torch.int8).reshape(-1)
+                pin = pin.expand(B).contiguous() if pin.numel() == 1 else pin.contiguous()
+            with v._on_device():
+                _cabi.check(self._lib.oth_selfplay_new_game(v._state(), self._c_sp, B, v.board_size, v.seed_value,
+                                                            v.env_id_base, self.test_rand_steps, self._game_index,
+                                                            _cabi.ptr(pin), v._stream()), "oth_selfplay_new_game")
+            self._game_index += 1
+            saved_rand = v.initial_rand_steps
+            v.initial_rand_steps = self.test_rand_steps                 # :372
+            try:
+                v.refresh_outputs()
+                P = self.protagonist.clone()
+                for ply in range(N - 4):                                 # every valid ply fills one cell
+                    turn = v.player_turn.clone()
+                    live = ~v.terminated()
+                    with torch.no_grad():
+                        _, actions, _, _ = policy.act(v.obs, ex_hiddens, ones, self._choices_arg(v.legal_mask))
+                    a = self._as_dev(actions, torch.int64)
+                    scripted = v.policy_actions(name)
+                    mine = turn == P
+                    v.step(torch.where(mine, a, scripted))
+                    sign = torch.where(mine, 1.0, -1.0)
+                    wins += (live & v.done & (v.reward * sign > 0)).to(torch.int64)   # :432-439
+                    if ply % 8 == 7 and bool(v.terminated().all().item()):
+                        break
+            finally:
+                v.initial_rand_steps = saved_rand                        # :440
+        return per * B, int(wins.sum().item())
+
+
+class Envs(_RuleBaseGames):
     """envs.py:7-41.  `envs`: an int (number of lockstep envs) or, drop-in style, a list of
     env objects whose first element supplies board_size / initial_rand_steps /
     num_disk_as_reward / rand_seed / test_rand_steps_holder (ppo_run_self_play.py:99-109);
@@ -215,41 +260,164 @@ class PPOEnvs(Envs):
         """envs.py:229-257 + rule_base_game (ppo_run_self_play.py:371-441): the learner plays
         `num_games // num_envs` games per env against 'rand' | 'greedy' with the test opening
         budget; a win = final reward from the learner's side > 0.  -> (games, wins)."""
-        if name not in ("rand", "greedy"):
-            raise ValueError("test opponent must be 'rand' or 'greedy'")
+        return self._rule_base_games(self.policy, name, num_games, ex_hiddens, protagonists)
+
+
+class WhoList(object):
+    """``t_or_s`` of PPOTeacherStudentEnvs.step: uint8 CUDA tensor (0 = teacher, 1 = student) that iterates
+    as the reference's list of 'teacher' / 'student' strings (envs.py:122-134)."""
+
+    def __init__(self, who_u8):
+        self.who = who_u8
+
+    @property
+    def is_teacher(self):
+        return self.who == 0
+
+    def __len__(self):
+        return self.who.numel()
+
+    def __getitem__(self, i):
+        return "teacher" if int(self.who[i].item()) == 0 else "student"
+
+    def __iter__(self):
+        for w in self.who.cpu().tolist():
+            yield "teacher" if w == 0 else "student"
+
+
+class TeacherStudentInfos(SelfPlayInfos):
+    """infos of one PPOTeacherStudentEnvs.step: ``.type`` uint8 [B] (0 = 'black_transition', 1 =
+    'white_transition', 2 = 'over'), ``.choices_mask`` bool [B, S*S]; dict access builds the reference's
+    {'type', 'choices'} lazily."""
+    _NAMES = ("black_transition", "white_transition", "over")
+
+    def __getitem__(self, i):
+        return {"type": self._NAMES[int(self.type[i].item())],
+                "choices": torch.nonzero(self.choices_mask[i]).flatten().tolist()}
+
+    def __iter__(self):
+        types = self.type.cpu().tolist()
+        masks = self.choices_mask.cpu()
+        for t, m in zip(types, masks):
+            yield {"type": self._NAMES[t], "choices": torch.nonzero(m).flatten().tolist()}
+
+
+class PPOTeacherStudentEnvs(Envs):
+    """envs.py:44-184 (teacher vs student) + the worker othello_teacher_vs_student
+    (ppo_run_teacher_vs_student.py:425-573), on the device.
+
+    Both colours learn: every ``step`` returns, per env, ONE tuple -- a black or a white transition (or
+    'over') -- labelled teacher / student by colour.  Inside a call the reference serves all pending
+    ``need_black_action`` requests before the white ones (envs.py:78) with ``policy[turn].act`` on the whole
+    batch; here each such act is followed by one ``oth_ts_advance`` launch for that colour.  The tensors
+    returned are bit-identical to the live reference's (tests/test_gpu_teacher_student.py, golden from real
+    forked workers).  Tensor-typed returns as in PPOEnvs: ``t_or_s`` is a WhoList, ``dones`` a bool tensor,
+    ``infos`` a TeacherStudentInfos."""
+
+    def __init__(self, envs, subproc_worker=None, teacher_policy=None, student_policy=None, device=None, **kw):
+        super(PPOTeacherStudentEnvs, self).__init__(envs, subproc_worker, teacher_policy, device, **kw)
+        self.teacher_policy = teacher_policy
+        self.student_policy = student_policy
+        self.teacher = None
+        self.student = None
+        self.policy = {}
+        self.int_to_str = {-1: "black", 1: "white"}
+        self._teacher_done_reward = 0.0
+        S, N, B, W, dev = self.board_size, self.num_actions, self.num_processes, self.vec.words, self.device
+        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)   # noqa: E731
+        self._ts_phase = z((B,), torch.uint8)
+        self._ts_sav = {k: z((2, W, B), torch.int64) for k in ("black", "white", "legal", "choices")}
+        self._ts_sav_meta = z((2, B), torch.int32)
+        self._ts_sav_action = z((2, B), torch.int64)
+        self._ts_sav_outputs = z((2, B, 3), torch.float32)
+        self._ts_queued_reward = z((B,), torch.int32)
+        self._ts_tr = {k: z((W, B), torch.int64) for k in ("black", "white", "legal", "choices")}
+        self._ts_tr_meta = z((B,), torch.int32)
+        self._ts_tr_action = z((B,), torch.int64)
+        self._ts_tr_reward = z((B,), torch.float32)
+        self._ts_tr_done = z((B,), torch.uint8)
+        self._ts_tr_type = z((B,), torch.uint8)
+        self._ts_tr_who = z((B,), torch.uint8)
+        self._ts_tr_outputs = z((B, 3), torch.float32)
+        self._ts_need = z((2,), torch.int32)
+        self._c_ts = _cabi.OthTeacherStudent(*[_cabi.ptr(t) for t in (
+            self._ts_phase, self._ts_sav["black"], self._ts_sav["white"], self._ts_sav["legal"], self._ts_sav_meta,
+            self._ts_sav["choices"], self._ts_sav_action, self._ts_sav_outputs, self._ts_queued_reward,
+            self._ts_tr["black"], self._ts_tr["white"], self._ts_tr["legal"], self._ts_tr["choices"], self._ts_tr_meta,
+            self._ts_tr_action, self._ts_tr_reward, self._ts_tr_done, self._ts_tr_type, self._ts_tr_who,
+            self._ts_tr_outputs)])
+        self._c_ts_state = _cabi.OthState(_cabi.ptr(self._ts_tr["black"]), _cabi.ptr(self._ts_tr["white"]),
+                                          _cabi.ptr(self._ts_tr["legal"]), _cabi.ptr(self._ts_tr_meta),
+                                          _cabi.ptr(self._dummy_ctr))
+        self._c_ts_choice_state = _cabi.OthState(_cabi.ptr(self._ts_tr["black"]), _cabi.ptr(self._ts_tr["white"]),
+                                                 _cabi.ptr(self._ts_tr["choices"]), _cabi.ptr(self._ts_tr_meta),
+                                                 _cabi.ptr(self._dummy_ctr))
+        self.policy_calls = []
+
+    def reset(self, teacher, win_avg, last_win_avg):
+        """envs.py:54-61 + the worker's 'reset' (:444-455).  teacher = -1 | +1."""
+        teacher = int(teacher)
+        if teacher not in (-1, 1):
+            raise ValueError("teacher must be -1 (black) or +1 (white)")
+        self.teacher = teacher
+        self.student = -teacher
+        self.policy = {self.teacher: self.teacher_policy, self.student: self.student_policy}
+        r = 0
+        for k in win_avg.keys():                                         # :459-461, same accumulation order
+            r += win_avg[k] - last_win_avg[k]
+        self._teacher_done_reward = float(r)
         v = self.vec
-        B, N = self.num_processes, v.num_cells
-        per = int(num_games) // B
-        wins = torch.zeros((B,), dtype=torch.int64, device=self.device)
-        ones = torch.ones((B, 1), dtype=torch.float32, device=self.device)
-        for g in range(per):
-            pin = None
-            if protagonists is not None:
-                pin = torch.as_tensor(protagonists[g]).to(device=self.device, dtype=torch.int8).reshape(-1)
-                pin = pin.expand(B).contiguous() if pin.numel() == 1 else pin.contiguous()
-            with v._on_device():
-                _cabi.check(self._lib.oth_selfplay_new_game(v._state(), self._c_sp, B, v.board_size, v.seed_value,
-                                                            v.env_id_base, self.test_rand_steps, self._game_index,
-                                                            _cabi.ptr(pin), v._stream()), "oth_selfplay_new_game")
-            self._game_index += 1
-            saved_rand = v.initial_rand_steps
-            v.initial_rand_steps = self.test_rand_steps                 # :372
-            try:
-                v.refresh_outputs()
-                P = self.protagonist.clone()
-                for ply in range(N - 4):                                 # every valid ply fills one cell
-                    turn = v.player_turn.clone()
-                    live = ~v.terminated()
-                    with torch.no_grad():
-                        _, actions, _, _ = self.policy.act(v.obs, ex_hiddens, ones, self._choices_arg(v.legal_mask))
-                    a = self._as_dev(actions, torch.int64)
-                    scripted = v.policy_actions(name)
-                    mine = turn == P
-                    v.step(torch.where(mine, a, scripted))
-                    sign = torch.where(mine, 1.0, -1.0)
-                    wins += (live & v.done & (v.reward * sign > 0)).to(torch.int64)   # :432-439
-                    if ply % 8 == 7 and bool(v.terminated().all().item()):
-                        break
-            finally:
-                v.initial_rand_steps = saved_rand                        # :440
-        return per * B, int(wins.sum().item())
+        with v._on_device():
+            _cabi.check(self._lib.oth_ts_new_game(v._state(), self._c_ts, self.num_processes, v.board_size,
+                                                  v.seed_value, v.env_id_base, v.initial_rand_steps, v._stream()),
+                        "oth_ts_new_game")
+
+    def step(self, ex_hiddens_student, ex_hiddens_teacher):
+        if self.teacher is None:
+            raise RuntimeError("call reset(teacher, win_avg, last_win_avg) first")
+        v = self.vec
+        B = self.num_processes
+        flags = self._flags()
+        tdr = self._teacher_done_reward
+        self.policy_calls = []
+        with v._on_device():
+            _cabi.check(self._lib.oth_ts_begin(v._state(), self._c_ts, B, v.board_size, flags, self.teacher, tdr,
+                                               v._outputs(with_scalars=False), _cabi.ptr(self._ts_need), v._stream()),
+                        "oth_ts_begin")
+            need_b, need_w = (int(x) for x in self._ts_need.tolist())
+            while need_b > 0 or need_w > 0:                              # envs.py:76
+                turn = -1 if need_b > 0 else 1                           # envs.py:78
+                ex_hiddens = ex_hiddens_teacher if turn == self.teacher else ex_hiddens_student
+                emitted = (self._ts_phase & _cabi.TS_EMITTED) != 0
+                masks = torch.where(emitted, 1.0 - self._ts_tr_done.float(),
+                                    torch.ones((), device=self.device)).unsqueeze(1)
+                with torch.no_grad():
+                    value, actions, logp, hidden = self.policy[turn].act(v.obs, ex_hiddens, masks,
+                                                                         self._choices_arg(v.legal_mask))   # :83
+                self.policy_calls.append(turn)
+                a = self._as_dev(actions, torch.int64)
+                val, lp, hid = (self._as_dev(x, torch.float32) for x in (value, logp, hidden))
+                if a.numel() != B or val.numel() != B or lp.numel() != B or hid.numel() != B:
+                    raise ValueError("policy.act must return one value / action / log-prob / hidden per env")
+                _cabi.check(self._lib.oth_ts_advance(v._state(), self._c_ts, B, v.board_size, flags, self.teacher, tdr,
+                                                     turn, _cabi.ptr(a), _cabi.ptr(val), _cabi.ptr(lp), _cabi.ptr(hid),
+                                                     v.seed_value, v.env_id_base, v.initial_rand_steps,
+                                                     v._outputs(with_scalars=False), _cabi.ptr(self._ts_need),
+                                                     v._stream()), "oth_ts_advance")
+                need_b, need_w = (int(x) for x in self._ts_need.tolist())
+            zf = (flags | _cabi.F_ZERO_IF_TERMINATED) & ~_cabi.F_AUTO_RESET
+            _cabi.check(self._lib.oth_observe(self._c_ts_state, B, v.board_size, zf, self._c_tr_obs_out, v._stream()),
+                        "oth_observe")
+            _cabi.check(self._lib.oth_observe(self._c_ts_choice_state, B, v.board_size, zf, self._c_tr_choice_out,
+                                              v._stream()), "oth_observe")
+        dones = self._ts_tr_done.view(torch.bool)
+        masks = (1.0 - self._ts_tr_done.float()).unsqueeze(1)            # envs.py:99
+        bad_masks = torch.ones((B, 1), dtype=torch.float32, device=self.device)   # envs.py:100
+        infos = TeacherStudentInfos(self._ts_tr_type, self._tr_choices_u8.view(torch.bool))
+        return (WhoList(self._ts_tr_who), self._tr_obs, self._ts_tr_action.float().unsqueeze(1),
+                self._ts_tr_reward.unsqueeze(1), dones, infos, self._ts_tr_outputs, masks, bad_masks)
+
+    def test(self, name, num_games, ex_hiddens, teacher=False, protagonists=None):
+        """envs.py:142-184: rule_base_game with the teacher's or the student's network.  -> (games, wins)"""
+        policy = self.teacher_policy if teacher else self.student_policy
+        return self._rule_base_games(policy, name, num_games, ex_hiddens, protagonists)

@@ -228,6 +228,69 @@ int oth_selfplay_advance(oth_state st, oth_selfplay sp, int64_t B, int board_siz
                          const float *value, const float *logp, const float *hidden, uint64_t seed,
                          int64_t env_id_base, int init_rand_steps, oth_outputs out, int32_t *need_count, void *stream);
 
+/* ---- teacher / student protocol (envs.py:44-140 PPOTeacherStudentEnvs.step, ppo_run_teacher_vs_student.py:
+ * 425-560 othello_teacher_vs_student) --------------------------------------------------------------------------
+ * Both colours are learners.  Per env and colour c (index 0 = black, 1 = white) the engine keeps c's latest
+ * decision; arrays marked [2] are colour-major: element (c, k, i) at ((c * W) + k) * B + i for bitboards,
+ * (c * B + i) for scalars.  The tuple an env owes per step() call is assembled in tr_*:
+ *   - c moves again because the other side must pass: c's tuple, c's own reward, done 0      (:486-488 / :529-531)
+ *   - c's run ends: the OTHER colour's tuple with minus c's last reward and c's done flag      (:498-503 / :541-545);
+ *     when the game is over c's own tuple follows in the NEXT call (OTH_TS_QUEUED)            (:505-509 / :546-551);
+ *     with nothing pending on the other side (white before its first move) it is emitted at once
+ *   - finished env: zeros, done 1, type OTH_TS_TYPE_OVER, no choices                          (:470-471)
+ * The saved state of c is taken when c's run of plies STARTS and kept through forced-pass runs (reference quirk;
+ * OTH_F_SP_FRESH_STATE refreshes it on every ply).  The teacher colour's reward is replaced by
+ * teacher_done_reward when the tuple's done flag is set, else 0 (:457-466).
+ * Observation planes of the tuple: oth_observe on {tr_black, tr_white, tr_legal, tr_meta} with
+ * OTH_F_ZERO_IF_TERMINATED; its choices: the same call on {.., tr_choices, ..}. */
+typedef struct oth_teacher_student {
+    uint8_t  *phase;          /* [B] OTH_TS_* bits */
+    uint64_t *sav_black;      /* [2][W][B] board of c's saved state */
+    uint64_t *sav_white;      /* [2][W][B] */
+    uint64_t *sav_legal;      /* [2][W][B] legal set of that state (the planes4 legal plane) */
+    uint32_t *sav_meta;       /* [2][B]    turn bit of that state */
+    uint64_t *sav_choices;    /* [2][W][B] possible_moves at c's latest decision */
+    int64_t  *sav_action;     /* [2][B] */
+    float    *sav_outputs;    /* [2][B][3] value, log-prob, hidden of c's latest decision */
+    int32_t  *queued_reward;  /* [B] raw reward of the queued final tuple */
+    uint64_t *tr_black, *tr_white, *tr_legal, *tr_choices;   /* [W][B] the emitted tuple's state / choices */
+    uint32_t *tr_meta;        /* [B] turn bit, or OTH_META_TERMINATED for an all-zero tuple */
+    int64_t  *tr_action;      /* [B] */
+    float    *tr_reward;      /* [B] */
+    uint8_t  *tr_done;        /* [B] */
+    uint8_t  *tr_type;        /* [B] OTH_TS_TYPE_* */
+    uint8_t  *tr_who;         /* [B] 0 = teacher, 1 = student (envs.py:122-134; 'over' rows count as white) */
+    float    *tr_outputs;     /* [B][3] */
+} oth_teacher_student;
+
+#define OTH_TS_EMITTED      0x01  /* this env has produced its tuple for the current call */
+#define OTH_TS_FINISHED     0x02  /* game over */
+#define OTH_TS_PEND_BLACK   0x04  /* black has a decision waiting for its reward */
+#define OTH_TS_PEND_WHITE   0x08
+#define OTH_TS_PREV_BLACK   0x10  /* colour of the previous ply of this game (neither bit: no ply yet) */
+#define OTH_TS_PREV_WHITE   0x20
+#define OTH_TS_QUEUED       0x40  /* the last mover's own final tuple is owed at the next call */
+#define OTH_TS_QUEUED_WHITE 0x80  /* ... and that mover was white */
+#define OTH_TS_TYPE_BLACK 0   /* 'black_transition' */
+#define OTH_TS_TYPE_WHITE 1   /* 'white_transition' */
+#define OTH_TS_TYPE_OVER  2   /* 'over' */
+
+/* The worker's 'reset' (:444-455): new game in every env, all protocol state cleared. */
+int oth_ts_new_game(oth_state st, oth_teacher_student ts, int64_t B, int board_size, uint64_t seed,
+                    int64_t env_id_base, int init_rand_steps, void *stream);
+/* Start of a step() call: clears OTH_TS_EMITTED; finished envs emit their queued final tuple or an 'over' row.
+ * teacher = -1 | +1 (colour of the teacher this episode).  Writes out.obs / out.legal_mask for the current states
+ * and need_count[0] / need_count[1] = number of envs waiting for a BLACK / WHITE action. */
+int oth_ts_begin(oth_state st, oth_teacher_student ts, int64_t B, int board_size, int flags, int teacher,
+                 float teacher_done_reward, oth_outputs out, int32_t *need_count, void *stream);
+/* One policy[colour].act worth of progress (envs.py:83-98): every env still owing a tuple whose side to move is
+ * `colour` records (actions[i], value[i], logp[i], hidden[i]) as that colour's decision and plays it (subject to
+ * the random-opening override, othello.py:70-73).  Same outputs as oth_ts_begin. */
+int oth_ts_advance(oth_state st, oth_teacher_student ts, int64_t B, int board_size, int flags, int teacher,
+                   float teacher_done_reward, int colour, const int64_t *actions, const float *value,
+                   const float *logp, const float *hidden, uint64_t seed, int64_t env_id_base, int init_rand_steps,
+                   oth_outputs out, int32_t *need_count, void *stream);
+
 /* Legal-move-restricted categorical over the learner's logits (model.py:60-150 Policy.act, :156-198
  * evaluate_actions): the distribution is softmax(logits[i][choices_i]), choices_i = set bits of legal[.][i].
  *   mode OTH_CAT_SAMPLE    action ~ that distribution (inverse CDF in ascending action order, one Philox draw,
