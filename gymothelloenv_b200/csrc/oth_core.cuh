@@ -11,8 +11,9 @@
 //   env_reset()  othello.py:256-271 + :62-64 (opening budget)
 //   greedy_pick  simple_policies.py:69-92
 //   maximin_pick simple_policies.py:111-163
-// The algorithm is NOT the reference's cell-by-cell ray walk: moves and flips come from
-// 8 directional Kogge-Stone occluded fills (shift + mask), popcounts give the scores.
+// The algorithm is NOT the reference's cell-by-cell ray walk: east/west moves and all flips come
+// from carry propagation (an add ripples through a run of opponent discs), the other move axes
+// from paired Kogge-Stone occluded fills (shift + mask); popcounts give the scores.
 #pragma once
 #include <stdint.h>
 #include "../../include/othello_b200.h"
@@ -54,12 +55,6 @@ constexpr u64 geo_word_of_cells(int S, int wi, int a0, int a1, int a2, int a3) {
         if (cells[k] >= 0 && cells[k] / 64 == wi) m |= 1ull << (cells[k] % 64);
     return m;
 }
-constexpr int geo_rounds(int S) {   // smallest R with 2^R - 1 >= S - 2 (longest bracketed run)
-    int r = 1;
-    while ((1 << r) - 1 < S - 2) r++;
-    return r;
-}
-
 template <int S, int WI>
 struct GeoWord {
     static constexpr int c = S / 2;
@@ -77,7 +72,6 @@ template <int S>
 struct Geo {
     static constexpr int N = S * S;
     static constexpr int W = (N + 63) / 64;
-    static constexpr int ROUNDS = geo_rounds(S);
     static_assert(S >= OTH_MIN_BOARD_SIZE && S <= 16, "board size out of range");
 };
 
@@ -151,35 +145,6 @@ OTH_DEV BB<W> sh(const BB<W> &a) {
     else return shr<K, W>(a);
 }
 
-// Kogge-Stone occluded fill: gen plus every cell reachable from gen by stepping STEP in
-// one direction through cells of pro only.  ROUNDS doublings cover runs of S-2 discs.
-template <int S, int STEP, bool LEFT>
-OTH_DEV BB<Geo<S>::W> kfill(BB<Geo<S>::W> gen, BB<Geo<S>::W> pro) {
-    constexpr int R = Geo<S>::ROUNDS;
-    constexpr int W = Geo<S>::W;
-    gen = gen | (pro & sh<STEP, LEFT, W>(gen));
-    if constexpr (R > 1) {
-        pro = pro & sh<STEP, LEFT, W>(pro);
-        gen = gen | (pro & sh<2 * STEP, LEFT, W>(gen));
-    }
-    if constexpr (R > 2) {
-        pro = pro & sh<2 * STEP, LEFT, W>(pro);
-        gen = gen | (pro & sh<4 * STEP, LEFT, W>(gen));
-    }
-    if constexpr (R > 3) {
-        pro = pro & sh<4 * STEP, LEFT, W>(pro);
-        gen = gen | (pro & sh<8 * STEP, LEFT, W>(gen));
-    }
-    return gen;
-}
-
-template <int S, int STEP, bool LEFT>
-OTH_DEV BB<Geo<S>::W> dir_moves(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &pro) {
-    constexpr int W = Geo<S>::W;
-    BB<W> run = kfill<S, STEP, LEFT>(own, pro) & pro;   // bracket-able opponent runs next to own discs
-    return sh<STEP, LEFT, W>(run);
-}
-
 // ---- single-word boards (S <= 8): legal moves -----------------------------------------
 // East: adding the cells just east of own discs to the inner-column opponent mask makes
 // the carry ripple through each bracket-able run and land on the cell behind it (edge
@@ -214,6 +179,80 @@ OTH_DEV u64 legal1(u64 P, u64 O) {
     else return moves & ~(P | O) & GeoWord<S, 0>::full;
 }
 
+// ---- multi-word boards (S = 9..12, W = 2..3): whole-board arithmetic --------------------
+// The single-word tricks carry over once add / subtract / bit-reverse work on the whole W-word
+// board: a row is still S contiguous bits (it may straddle a word boundary, which is why the
+// carry must run through all words), and the bit-reversed board still has contiguous rows.
+template <int W> OTH_DEV BB<W> bb_add(const BB<W> &a, const BB<W> &b) {
+    BB<W> r;
+    if constexpr (W == 1) {
+        r.w[0] = a.w[0] + b.w[0];
+    } else if constexpr (W == 2) {
+        asm("add.cc.u64 %0, %2, %4;\n\taddc.u64 %1, %3, %5;"
+            : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(a.w[0]), "l"(a.w[1]), "l"(b.w[0]), "l"(b.w[1]));
+    } else if constexpr (W == 3) {
+        asm("add.cc.u64 %0, %3, %6;\n\taddc.cc.u64 %1, %4, %7;\n\taddc.u64 %2, %5, %8;"
+            : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2])
+            : "l"(a.w[0]), "l"(a.w[1]), "l"(a.w[2]), "l"(b.w[0]), "l"(b.w[1]), "l"(b.w[2]));
+    } else {
+        static_assert(W == 4, "bb_add: W <= 4");
+        asm("add.cc.u64 %0, %4, %8;\n\taddc.cc.u64 %1, %5, %9;\n\taddc.cc.u64 %2, %6, %10;\n\taddc.u64 %3, %7, %11;"
+            : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3])
+            : "l"(a.w[0]), "l"(a.w[1]), "l"(a.w[2]), "l"(a.w[3]), "l"(b.w[0]), "l"(b.w[1]), "l"(b.w[2]), "l"(b.w[3]));
+    }
+    return r;
+}
+template <int W> OTH_DEV BB<W> bb_sub(const BB<W> &a, const BB<W> &b) {
+    BB<W> r;
+    if constexpr (W == 1) {
+        r.w[0] = a.w[0] - b.w[0];
+    } else if constexpr (W == 2) {
+        asm("sub.cc.u64 %0, %2, %4;\n\tsubc.u64 %1, %3, %5;"
+            : "=l"(r.w[0]), "=l"(r.w[1]) : "l"(a.w[0]), "l"(a.w[1]), "l"(b.w[0]), "l"(b.w[1]));
+    } else if constexpr (W == 3) {
+        asm("sub.cc.u64 %0, %3, %6;\n\tsubc.cc.u64 %1, %4, %7;\n\tsubc.u64 %2, %5, %8;"
+            : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2])
+            : "l"(a.w[0]), "l"(a.w[1]), "l"(a.w[2]), "l"(b.w[0]), "l"(b.w[1]), "l"(b.w[2]));
+    } else {
+        static_assert(W == 4, "bb_sub: W <= 4");
+        asm("sub.cc.u64 %0, %4, %8;\n\tsubc.cc.u64 %1, %5, %9;\n\tsubc.cc.u64 %2, %6, %10;\n\tsubc.u64 %3, %7, %11;"
+            : "=l"(r.w[0]), "=l"(r.w[1]), "=l"(r.w[2]), "=l"(r.w[3])
+            : "l"(a.w[0]), "l"(a.w[1]), "l"(a.w[2]), "l"(a.w[3]), "l"(b.w[0]), "l"(b.w[1]), "l"(b.w[2]), "l"(b.w[3]));
+    }
+    return r;
+}
+template <int W> OTH_DEV BB<W> bb_one(u64 v) { BB<W> r; BB_FOR(i) r.w[i] = i == 0 ? v : 0ull; return r; }
+// bit j -> bit 64*W - 1 - j
+template <int W> OTH_DEV BB<W> bb_brev(const BB<W> &a) { BB<W> r; BB_FOR(i) r.w[i] = __brevll(a.w[W - 1 - i]); return r; }
+
+// East / west moves of a multi-word board by carry propagation (see legal1); Oi = opponent discs in
+// the inner columns, in the same (normal or reversed) bit order as P.
+template <int W> OTH_DEV BB<W> carry_moves(const BB<W> &P, const BB<W> &Oi) {
+    return andnot(bb_add<W>(Oi, shl<1, W>(P) & Oi), Oi);
+}
+// The three other axes: paired Kogge-Stone fills sharing the doubled propagators between the two
+// opposite directions; reach after the rounds: 2, 4, 8, 12 cells (the longest run is S-2 <= 10).
+template <int S, int D>
+OTH_DEV BB<Geo<S>::W> pair_moves(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &m) {
+    constexpr int W = Geo<S>::W;
+    BB<W> fl = m & shl<D, W>(P), fr = m & shr<D, W>(P);
+    fl = fl | (m & shl<D, W>(fl));
+    fr = fr | (m & shr<D, W>(fr));
+    const BB<W> pl = m & shl<D, W>(m), pr = shr<D, W>(pl);
+    fl = fl | (pl & shl<2 * D, W>(fl));
+    fr = fr | (pr & shr<2 * D, W>(fr));
+    if constexpr (S - 2 > 4) {
+        const BB<W> pl2 = pl & shl<2 * D, W>(pl), pr2 = pr & shr<2 * D, W>(pr);
+        fl = fl | (pl2 & shl<4 * D, W>(fl));
+        fr = fr | (pr2 & shr<4 * D, W>(fr));
+        if constexpr (S - 2 > 8) {
+            fl = fl | (pl2 & shl<4 * D, W>(fl));
+            fr = fr | (pr2 & shr<4 * D, W>(fr));
+        }
+    }
+    return shl<D, W>(fl) | shr<D, W>(fr);
+}
+
 // othello.py:313-343: empty cells from which >=1 direction holds a run of opponent discs
 // closed by an own disc.
 template <int S>
@@ -223,25 +262,15 @@ OTH_DEV BB<Geo<S>::W> legal(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) 
         BB<W> r;
         r.w[0] = legal1<S>(own.w[0], opp.w[0]);
         return r;
+    } else {
+        const BB<W> Oi = opp & geo_inner<S>();
+        BB<W> m = carry_moves<W>(own, Oi);
+        m = m | bb_brev<W>(carry_moves<W>(bb_brev<W>(own), bb_brev<W>(Oi)));
+        m = m | pair_moves<S, S>(own, opp);
+        m = m | pair_moves<S, S - 1>(own, Oi);
+        m = m | pair_moves<S, S + 1>(own, Oi);
+        return andnot(m & geo_full<S>(), own | opp);
     }
-    const BB<W> inner = opp & geo_inner<S>();
-    BB<W> m = dir_moves<S, 1, true>(own, inner);
-    m = m | dir_moves<S, 1, false>(own, inner);
-    m = m | dir_moves<S, S, true>(own, opp);
-    m = m | dir_moves<S, S, false>(own, opp);
-    m = m | dir_moves<S, S + 1, true>(own, inner);
-    m = m | dir_moves<S, S + 1, false>(own, inner);
-    m = m | dir_moves<S, S - 1, true>(own, inner);
-    m = m | dir_moves<S, S - 1, false>(own, inner);
-    return andnot(m & geo_full<S>(), own | opp);
-}
-
-template <int S, int STEP, bool LEFT>
-OTH_DEV BB<Geo<S>::W> dir_flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &pro) {
-    constexpr int W = Geo<S>::W;
-    BB<W> flood = kfill<S, STEP, LEFT>(mv, pro);
-    BB<W> closed = sh<STEP, LEFT, W>(flood) & own;   // the cell after the run holds an own disc
-    return bb_select(any(closed), flood & pro, bb_zero<W>());
 }
 
 // ---- single-word boards (S <= 8): flips by carry propagation ---------------------------
@@ -290,29 +319,85 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
     return up | __brevll(dn);
 }
 
-// othello.py:391-410: discs turned by placing an own disc on the single cell `mv`
-// (mv == 0 gives 0, which is how invalid moves stay branch-free).
+// ---- multi-word boards: flips by carry propagation -------------------------------------
+// whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
+template <int W> OTH_DEV BB<W> bb_shl_var(const BB<W> &x, int a) {
+    const int q = a >> 6, b = a & 63;
+    BB<W> s;                                             // x << b
+    BB_FOR(i) {
+        const u64 lo = i > 0 ? x.w[i > 0 ? i - 1 : 0] : 0ull;
+        s.w[i] = (x.w[i] << b) | ((lo >> 1) >> (63 - b));
+    }
+    BB<W> r;                                             // then q whole words
+    BB_FOR(i) {
+        u64 v = 0ull;
+        BB_FOR(j) { if (j <= i) v = (q == i - j) ? s.w[j] : v; }
+        r.w[i] = v;
+    }
+    return r;
+}
+constexpr u64 geo_word_ray_pattern(int S, int D, int wi) {   // cells D, 2D, ..., (S-1)D
+    u64 m = 0;
+    for (int k = 1; k < S; k++) {
+        const int c = k * D;
+        if (c / 64 == wi) m |= 1ull << (c % 64);
+    }
+    return m;
+}
+template <int S, int D, int WI>
+struct GeoRayWord {
+    static constexpr u64 v = geo_word_ray_pattern(S, D, WI);
+};
+template <int S, int D> OTH_DEV BB<Geo<S>::W> geo_ray() {
+    BB<Geo<S>::W> r;
+    r.w[0] = GeoRayWord<S, D, 0>::v;
+    if constexpr (Geo<S>::W > 1) r.w[1] = GeoRayWord<S, D, 1>::v;
+    if constexpr (Geo<S>::W > 2) r.w[2] = GeoRayWord<S, D, 2>::v;
+    if constexpr (Geo<S>::W > 3) r.w[3] = GeoRayWord<S, D, 3>::v;
+    return r;
+}
+// one ray with mask m (cells above the move, nearest first): see ray_flips1
+template <int W> OTH_DEV BB<W> ray_flips(const BB<W> &m, const BB<W> &P, const BB<W> &O) {
+    BB<W> x;
+    BB_FOR(i) x.w[i] = O.w[i] | ~m.w[i];
+    const BB<W> t = bb_add<W>(x, bb_one<W>(1ull));
+    BB<W> stop;
+    BB_FOR(i) stop.w[i] = t.w[i] & ~x.w[i] & P.w[i];       // 0 or the single closing own disc
+    const BB<W> d = bb_sub<W>(stop, bb_one<W>(any(stop) ? 1ull : 0ull));
+    return d & m;
+}
+// the four rays towards higher bit indices from cell a (mv = its bit): east needs no ray mask -- the
+// carry out of mv<<1 ripples through the inner-column opponent run and lands on the cell behind it
 template <int S>
-OTH_DEV BB<Geo<S>::W> flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
+OTH_DEV BB<Geo<S>::W> flips_up(int a, const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &O,
+                               const BB<Geo<S>::W> &Oi) {
+    constexpr int W = Geo<S>::W;
+    const BB<W> first = shl<1, W>(mv);
+    const BB<W> land = andnot(bb_add<W>(Oi, first), Oi) & P;
+    BB<W> f = bb_select(any(land), bb_sub<W>(land, first), bb_zero<W>());
+    f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S>(), a), P, O);
+    f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S + 1>(), a), P, Oi);
+    f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S - 1>(), a), P, Oi);
+    return f;
+}
+
+// othello.py:391-410: discs turned by placing an own disc on cell a (mv = its single bit, or 0 for
+// "no move": the result is then 0, which is how invalid moves stay branch-free).
+template <int S>
+OTH_DEV BB<Geo<S>::W> flips_at(int a, const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
     constexpr int W = Geo<S>::W;
     if constexpr (W == 1) {
         BB<W> f;
         f.w[0] = flips1<S>(mv.w[0], own.w[0], opp.w[0]);
         return f;
     } else {
-        const BB<W> inner = opp & geo_inner<S>();
-        BB<W> f = dir_flips<S, 1, true>(mv, own, inner);
-        f = f | dir_flips<S, 1, false>(mv, own, inner);
-        f = f | dir_flips<S, S, true>(mv, own, opp);
-        f = f | dir_flips<S, S, false>(mv, own, opp);
-        f = f | dir_flips<S, S + 1, true>(mv, own, inner);
-        f = f | dir_flips<S, S + 1, false>(mv, own, inner);
-        f = f | dir_flips<S, S - 1, true>(mv, own, inner);
-        f = f | dir_flips<S, S - 1, false>(mv, own, inner);
-        return f;
+        const BB<W> Oi = opp & geo_inner<S>();
+        const BB<W> up = flips_up<S>(a, mv, own, opp, Oi);
+        const BB<W> dn = flips_up<S>(64 * W - 1 - a, bb_brev<W>(mv), bb_brev<W>(own), bb_brev<W>(opp), bb_brev<W>(Oi));
+        const BB<W> f = up | bb_brev<W>(dn);
+        return bb_select(any(mv), f, bb_zero<W>());
     }
 }
-
 // position of the n-th (0-based) set bit, n < popc(x)
 OTH_DEV int nth_bit64(u64 x, int n) {
     int pos = 0;
@@ -352,6 +437,12 @@ OTH_DEV int lowest_bit(const BB<W> &x) {
     }
     return r;
 }
+// flips of the single cell `mv` when its index is not at hand (mv == 0 gives 0)
+template <int S>
+OTH_DEV BB<Geo<S>::W> flips(const BB<Geo<S>::W> &mv, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) {
+    return flips_at<S>(lowest_bit(mv), mv, own, opp);
+}
+
 template <int W>
 OTH_DEV void clear_bit(BB<W> &x, int a) {
     BB_FOR(i) x.w[i] &= ~((a >> 6) == i ? (1ull << (a & 63)) : 0ull);
@@ -463,7 +554,7 @@ OTH_DEV StepResult env_step(EnvRegs<S> &e, i64 action, int flags) {
     const int a = in_range ? (int)action : 0;
     const bool valid = in_range && bb_test(e.legal, a);        // against the CACHED list (:417)
     BB<W> mv = bb_select(valid, bb_bit<W>(a), bb_zero<W>());
-    BB<W> f = flips<S>(mv, own, opp);                          // update_board (:391-410)
+    BB<W> f = flips_at<S>(a, mv, own, opp);                    // update_board (:391-410)
     own = own | f | mv;
     opp = andnot(opp, f);
 
@@ -522,7 +613,7 @@ OTH_DEV int greedy_pick(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp, BB<G
     while (any(moves)) {
         int a = lowest_bit(moves);
         clear_bit(moves, a);
-        int cnt = popc(flips<S>(bb_bit<W>(a), own, opp));
+        int cnt = popc(flips_at<S>(a, bb_bit<W>(a), own, opp));
         if (cnt > best_cnt) { best_cnt = cnt; best = a; }
     }
     return best;
@@ -546,7 +637,7 @@ struct MaxiMin {
                 int a = lowest_bit(moves);
                 clear_bit(moves, a);
                 BB<W> mv = bb_bit<W>(a);
-                BB<W> f = flips<S>(mv, pl, op);
+                BB<W> f = flips_at<S>(a, mv, pl, op);
                 int v;
                 if constexpr (D == 1) {      // children are leaves: count without expanding them
                     int k = popc(f);
@@ -569,7 +660,7 @@ struct MaxiMin {
             int a = lowest_bit(moves);
             clear_bit(moves, a);
             BB<W> mv = bb_bit<W>(a);
-            BB<W> f = flips<S>(mv, own, opp);
+            BB<W> f = flips_at<S>(a, mv, own, opp);
             int v;
             if constexpr (D == 1) v = own_cnt + popc(f) + 1;
             else v = MaxiMin<S, D - 1>::value(andnot(opp, f), own | f | mv, false);

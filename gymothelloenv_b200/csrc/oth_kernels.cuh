@@ -980,7 +980,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_update_board(oth_state s, i64 B, 
     BB<W> own = bb_select(wm, e.white, e.black), opp = bb_select(wm, e.black, e.white);
     const BB<W> mv = bb_bit<W>((int)action);
     opp = andnot(opp, mv);                 // the reference overwrites the cell whatever it held
-    const BB<W> f = flips<S>(mv, own, opp);
+    const BB<W> f = flips_at<S>((int)action, mv, own, opp);
     own = own | f | mv;
     opp = andnot(opp, f);
     e.white = bb_select(wm, own, opp);
