@@ -344,6 +344,41 @@ OTH_DEV void nib_write_layout(int layout, void *base, i64 env0, int nenv, const 
     }
 }
 
+// Even sizes other than 8x8, int8 outputs, full warp: "slab" writer.  Phase 1: lane e expands its own
+// env, 4 cells at a time (nibble -> 4 bytes), into the warp's shared-memory slab at byte e*N -- already the
+// output order, so no consumer ever divides by N/4 (for N/4 odd, S = 6 and 10, the word stride between
+// lanes is odd: conflict-free).  Phase 2: the 32 lanes copy the 32*N-byte slab to global memory as 16-byte
+// vectors, 512 contiguous bytes per store instruction.
+template <int S, bool HAS_NEG>
+OTH_DEV void slab_expand(unsigned char *slab, int lane, const BB<Geo<S>::W> &pos, const BB<Geo<S>::W> &neg) {
+    constexpr int N = Geo<S>::N, G4 = N / 4;
+    static_assert(N % 4 == 0, "slab writer: even board sizes only");
+    u32 *dst = reinterpret_cast<u32 *>(slab + lane * N);
+#pragma unroll
+    for (int r = 0; r < G4; r++) {
+        const int k = r >> 4, sh = 4 * (r & 7);
+        const bool hi = (r & 8) != 0;
+        const u32 ph = hi ? (u32)(pos.w[k] >> 32) : (u32)pos.w[k];
+        u32 w = spread4((ph >> sh) & 0xFu);
+        if constexpr (HAS_NEG) {
+            const u32 nh = hi ? (u32)(neg.w[k] >> 32) : (u32)neg.w[k];
+            w = spread4((nh >> sh) & 0xFu) * 0xFFu + w;
+        }
+        dst[r] = w;
+    }
+}
+template <int S>
+OTH_DEV void slab_copy(const unsigned char *slab, void *base, i64 env0, int lane) {
+    constexpr int N = Geo<S>::N, CH = 2 * N;                       // 32*N bytes = 2N chunks of 16
+    const uint4 *src = reinterpret_cast<const uint4 *>(slab);
+    uint4 *dst = reinterpret_cast<uint4 *>(reinterpret_cast<char *>(base) + env0 * (i64)N);
+#pragma unroll
+    for (int k = 0; k < (CH + 31) / 32; k++) {
+        const int c = lane + 32 * k;
+        if (CH % 32 == 0 || c < CH) dst[c] = src[c];
+    }
+}
+
 template <int W>
 OTH_DEV void stage_nibbles(uint4 *dst, const BB<W> &x) {
     BB_FOR(k) dst[k] = nibble_bytes(x.w[k]);
@@ -362,6 +397,26 @@ OTH_DEV void emit_dense_nib(const EnvRegs<S> &e, bool active, bool zero_obs, boo
     const BB<W> lg = bb_select(live, e.legal, zero);
     const BB<W> lg_mask = bb_select(active && !zero_mask, e.legal, zero);
     const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
+    if constexpr (S != 8) {
+        const bool obs_slab = layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
+        if (warp_env0 + 32 <= B && (obs_slab || layout == OTH_OBS_NONE)) {   // warp-uniform
+            static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
+            unsigned char *slab = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
+            if (obs_slab) {                                                  // othello.py:363-369
+                slab_expand<S, true>(slab, lane, bb_select(tw, white, black), bb_select(tw, black, white));
+                __syncwarp();
+                slab_copy<S>(slab, out.obs, warp_env0, lane);
+                __syncwarp();
+            }
+            if (out.legal_mask != nullptr) {
+                slab_expand<S, false>(slab, lane, lg_mask, lg_mask);
+                __syncwarp();
+                slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
+                __syncwarp();
+            }
+            return;
+        }
+    }
     if (layout == OTH_OBS_BOARD || layout == OTH_OBS_BOARD_MASK) {           // othello.py:363-376
         stage_nibbles<W>(st.nib[NIB_POS0][lane], bb_select(tw, white, black));
         stage_nibbles<W>(st.nib[NIB_NEG0][lane], bb_select(tw, black, white));
