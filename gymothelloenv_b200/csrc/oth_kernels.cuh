@@ -9,6 +9,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "oth_core.cuh"
+#include "oth_coop_search.cuh"
 
 constexpr int OTH_BLOCK = 128;
 constexpr int OTH_WARPS = OTH_BLOCK / 32;
@@ -927,6 +928,8 @@ struct RolloutParams {
     int trace_stride;
 };
 
+// Whole games in registers, one thread per game, every decision per thread (random / greedy pairings, and
+// every multi-word board size).
 template <int S>
 __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
@@ -957,6 +960,93 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
                 r = env_step<S>(e, a, p.flags);
                 ply++;
             }
+            t_plies += ply;
+            t_black += r.winner < 0;
+            t_draw += r.winner == 0;
+            t_white += r.winner > 0;
+            if (p.game_result) p.game_result[game] = (int8_t)r.winner;
+            if (p.game_plies) p.game_plies[game] = (int16_t)ply;
+            if (p.game_counts) {
+                p.game_counts[2 * game] = (uint8_t)popc(e.black);
+                p.game_counts[2 * game + 1] = (uint8_t)popc(e.white);
+            }
+        }
+    }
+    // warp tree-reduce, one atomic per counter per warp into the (NCCL send) buffer
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        t_black += __shfl_down_sync(0xFFFFFFFFu, t_black, o);
+        t_draw += __shfl_down_sync(0xFFFFFFFFu, t_draw, o);
+        t_white += __shfl_down_sync(0xFFFFFFFFu, t_white, o);
+        t_plies += __shfl_down_sync(0xFFFFFFFFu, t_plies, o);
+    }
+    if ((threadIdx.x & 31) == 0 && p.tally != nullptr) {
+        if (t_black) atomicAdd(&p.tally[0], (unsigned long long)t_black);
+        if (t_draw) atomicAdd(&p.tally[1], (unsigned long long)t_draw);
+        if (t_white) atomicAdd(&p.tally[2], (unsigned long long)t_white);
+        if (t_plies) atomicAdd(&p.tally[3], (unsigned long long)t_plies);
+    }
+}
+
+// Whole games in registers, one thread per game.  The warp stays convergent per ply so that maximin
+// decisions (depth >= 2, single-word boards) can be searched lane-cooperatively (oth_coop_search.cuh);
+// random / opening / greedy moves are picked per thread.
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_rollout_coop(RolloutParams p) {
+    constexpr int W = Geo<S>::W;
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    const bool in_range = i < p.B;
+    u32 t_black = 0, t_draw = 0, t_white = 0, t_plies = 0;
+    EnvRegs<S> e = empty_env<S>();
+    for (int g = 0; g < p.games_per_env; g++) {
+        const i64 game = i * p.games_per_env + g;
+        if (in_range) env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+        int ply = 0;
+        StepResult r;
+        r.done = in_range ? 0 : 1; r.winner = 0; r.reward = 0; r.action = -1;
+        while (__any_sync(0xFFFFFFFFu, !r.done)) {
+            const bool live = !r.done;
+            const bool wm = e.meta & OTH_META_TURN_WHITE;
+            const oth_policy_spec spec = wm ? p.white : p.black;
+            const BB<W> own = bb_select(wm, e.white, e.black), opp = bb_select(wm, e.black, e.white);
+            int a = -1;
+            int coop_depth = 0;                                     // > 0: this lane's move comes from the shared search
+            if (live) {
+                const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);
+                if (opening || spec.kind == OTH_POLICY_RANDOM) {
+                    a = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                    e.ctr++;
+                    if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+                } else if (W == 1 && spec.kind == OTH_POLICY_MAXIMIN && spec.depth >= 2 && any(e.legal)) {
+                    coop_depth = min(spec.depth, 4);
+                } else {
+                    a = policy_pick<S>(spec.kind, spec.depth, own, opp, e.legal, 0u);
+                }
+            }
+            if constexpr (W == 1) {
+                __shared__ CoopScratch coop[OTH_WARPS];
+                CoopScratch &sc = coop[threadIdx.x >> 5];
+                const bool small_lists = p.flags & OTH_F_SEARCH_SMALL_LISTS;
+                if (__any_sync(0xFFFFFFFFu, coop_depth == 2)) {
+                    const int c = coop_maximin_pick<S, 2>(coop_depth == 2, own.w[0], opp.w[0], e.legal.w[0], sc, small_lists);
+                    if (coop_depth == 2) a = c;
+                }
+                if (__any_sync(0xFFFFFFFFu, coop_depth == 3)) {
+                    const int c = coop_maximin_pick<S, 3>(coop_depth == 3, own.w[0], opp.w[0], e.legal.w[0], sc, small_lists);
+                    if (coop_depth == 3) a = c;
+                }
+                if (__any_sync(0xFFFFFFFFu, coop_depth == 4)) {
+                    const int c = coop_maximin_pick<S, 4>(coop_depth == 4, own.w[0], opp.w[0], e.legal.w[0], sc, small_lists);
+                    if (coop_depth == 4) a = c;
+                }
+            }
+            if (live) {
+                if (p.trace != nullptr && ply < p.trace_stride) p.trace[game * p.trace_stride + ply] = (int16_t)a;
+                r = env_step<S>(e, a, p.flags);
+                ply++;
+            }
+        }
+        if (in_range) {
             t_plies += ply;
             t_black += r.winner < 0;
             t_draw += r.winner == 0;
@@ -1084,7 +1174,10 @@ struct SizeLaunch {
         return cudaGetLastError();
     }
     static cudaError_t rollout(const RolloutParams &p, cudaStream_t q) {
-        k_rollout<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        const bool searches = (p.black.kind == OTH_POLICY_MAXIMIN && p.black.depth >= 2) ||
+                              (p.white.kind == OTH_POLICY_MAXIMIN && p.white.depth >= 2);
+        if (Geo<S>::W == 1 && searches) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        else k_rollout<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
         return cudaGetLastError();
     }
     static cudaError_t set_board(oth_state s, i64 B, const int8_t *cells, const int8_t *persp, const int8_t *turn,

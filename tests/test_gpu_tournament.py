@@ -68,22 +68,40 @@ def _replay_games(S, black, white, init_rand, seed, base, rec, games):
     assert np.array_equal(counts[:, 1], (board == 1).reshape(games, -1).sum(1))
 
 
-@pytest.mark.parametrize("S,black,white,init_rand,games", [
+ROLLOUT_CASES = [
     (8, "rand", "greedy", 10, 512), (8, "greedy", "rand", 10, 512), (8, "greedy", "maximin2", 10, 192),
     (8, "maximin3", "greedy", 6, 40), (8, "rand", "rand", 0, 700), (6, "maximin3", "maximin2", 4, 128),
     (6, "maximin4", "rand", 0, 64), (10, "greedy", "rand", 10, 160), (12, "rand", "maximin2", 8, 48),
     (5, "maximin2", "greedy", 4, 200), (4, "maximin4", "maximin3", 2, 100), (9, "greedy", "greedy", 10, 64),
-])
-def test_rollout_games_rederived_on_host(S, black, white, init_rand, games):
+    (8, "maximin2", "maximin3", 10, 96), (8, "rand", "maximin4", 10, 33), (7, "maximin3", "maximin3", 2, 130),
+]
+
+
+def _check_rollout(S, black, white, init_rand, games, **kw):
     seed, base = 12345 + S, 7_000_000_000
     tally, rec = _rollout(games, black, white, board_size=S, initial_rand_steps=init_rand, seed=seed,
-                          env_id_base=base, record=True, trace_len=S * S + 8)
+                          env_id_base=base, record=True, trace_len=S * S + 8, **kw)
     torch.cuda.synchronize()
     _replay_games(S, black, white, init_rand, seed, base, rec, games)
     res = rec["result"].cpu().numpy()
     w, d, l, plies = tally.tolist()
     assert (w, d, l) == (int((res == -1).sum()), int((res == 0).sum()), int((res == 1).sum()))
     assert plies == int(rec["plies"].sum().item())
+
+
+@pytest.mark.parametrize("S,black,white,init_rand,games", ROLLOUT_CASES)
+def test_rollout_games_rederived_on_host(S, black, white, init_rand, games):
+    """Every action of every game against the oracle's policies (ragged last warps, mixed depths in one warp,
+    lane-cooperative maximin for S <= 8, per-thread DFS for S > 8)."""
+    _check_rollout(S, black, white, init_rand, games)
+
+
+@pytest.mark.parametrize("S,black,white,init_rand,games",
+                         [c for c in ROLLOUT_CASES if "maximin" in c[1] + c[2] and c[0] <= 8])
+def test_cooperative_search_fallback_rederived_on_host(S, black, white, init_rand, games):
+    """OTH_F_SEARCH_SMALL_LISTS: the cooperative search may keep only 3 root moves / 12 pairs, so most decisions
+    overflow and take the per-thread DFS fallback (depth 4: also mid-way through the root's moves)."""
+    _check_rollout(S, black, white, init_rand, games, search_small_lists=True)
 
 
 def test_sharding_invariance_and_multi_game_envs():
