@@ -32,10 +32,13 @@ struct CoopLevel2 {
     int val[COOP_CAP2];
     short first[COOP_CAP2 + 1];
 };
-// per warp: either one 32-lane group with both lists (depth >= 3) or four 8-lane groups with list 1 only
+// per warp: either one 32-lane group with both lists (depth >= 3) or 32 / COOP_GW2 narrow groups with list 1 only
+#ifndef COOP_GW2
+#define COOP_GW2 8          // lanes per game for depth 2 (4 measured within noise of 8: 2.91e7 vs 2.87e7 games/s)
+#endif
 union CoopScratch {
     struct { CoopLevel1 l1; CoopLevel2 l2; } wide;
-    CoopLevel1 narrow[4];
+    CoopLevel1 narrow[32 / COOP_GW2];
 };
 
 template <int GW> OTH_DEV u32 coop_group_mask(int lane) {
@@ -241,12 +244,12 @@ OTH_DEV int coop_pick_one(u64 own, u64 opp, u64 moves, CoopLevel1 &l1, CoopLevel
 template <int S, int D>
 __device__ __noinline__ int coop_maximin_pick(bool need, u64 own, u64 opp, u64 moves, CoopScratch &sc, bool small_lists) {
     static_assert(Geo<S>::W == 1, "cooperative search: single-word boards");
-    constexpr int GW = (D == 2) ? 8 : 32;
+    constexpr int GW = (D == 2) ? COOP_GW2 : 32;
     const int lane = threadIdx.x & 31, gl = lane & (GW - 1), gbase = lane & ~(GW - 1);
     const u32 gmask = coop_group_mask<GW>(lane);
     const u32 needing = __ballot_sync(0xFFFFFFFFu, need);
     u32 todo = (GW == 32) ? needing : ((needing >> gbase) & ((1u << GW) - 1u));
-    CoopLevel1 &l1 = (GW == 32) ? sc.wide.l1 : sc.narrow[lane / (GW == 32 ? 32 : GW) & 3];
+    CoopLevel1 &l1 = (GW == 32) ? sc.wide.l1 : sc.narrow[(lane / GW) % (32 / COOP_GW2)];
     CoopLevel2 *l2 = (GW == 32) ? &sc.wide.l2 : nullptr;
     const int cap1 = small_lists ? 3 : COOP_CAP1, cap2 = small_lists ? 12 : COOP_CAP2;   // OTH_F_SEARCH_SMALL_LISTS
     int result = -1;
