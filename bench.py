@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=30)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-timed-region", action="store_true",
+                    help="cudaProfilerStart/Stop around the K timed steps (ncu --profile-from-start off then lists "
+                         "exactly the launches of the timed region)")
     return ap.parse_args()
 
 
@@ -218,12 +221,17 @@ def run_ours(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_host0 = time.perf_counter()
+    done_total = torch.zeros((), dtype=torch.int64, device=dev)     # allocated before the timed region
+    torch.cuda.synchronize(dev)
+    if args.profile_timed_region:
+        torch.cuda.profiler.start()
     ev0.record()
-    done_total = torch.zeros((), dtype=torch.int64, device=dev)
     for _ in range(K):
         env.step(policy="random")
     ev1.record()
     barrier()
+    if args.profile_timed_region:
+        torch.cuda.profiler.stop()
     t_host1 = time.perf_counter()
     clocks = sampler.stop(t_host0, t_host1)
     ms_total = ev0.elapsed_time(ev1)

@@ -15,6 +15,9 @@ echo "== ncu launch list"
 $SHORT > $OUT/short_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv $SHORT > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
+echo "== ncu launch list of the TIMED REGION only (cudaProfilerStart/Stop around the K steps)"
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $OUT/launches_timed_region.csv $SHORT --profile-timed-region > $OUT/ncu_launches_timed.log 2>&1
+echo "ncu timed-region launches rc=$?"
 echo "== ncu full k_step"
 $SHORT > $OUT/short_plain2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:k_step -s 60 -c 3 -o $OUT/prof_step $SHORT > $OUT/ncu_full.log 2>&1

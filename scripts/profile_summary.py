@@ -8,8 +8,9 @@ src = os.path.join("gpurun_out", tag)
 os.makedirs("profiles", exist_ok=True)
 out = []
 
-def launches():
-    p = os.path.join(src, "launches.csv")
+def launches(fname="launches.csv", title="## ncu launch list (gpu__time_duration.sum, ns; cold-cache, serialised: compare shares)\n",
+             cmd="command: python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 (first 400 launches)\n"):
+    p = os.path.join(src, fname)
     if not os.path.isfile(p):
         return
     rows = list(csv.reader(open(p)))
@@ -23,8 +24,8 @@ def launches():
         if len(r) > vi:
             agg[r[ki][:70]].append(float(r[vi].replace(",", "")))
     tot = sum(sum(v) for v in agg.values())
-    out.append("## ncu launch list (gpu__time_duration.sum, ns; cold-cache, serialised: compare shares)\n")
-    out.append("command: python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 (first 400 launches)\n")
+    out.append(title)
+    out.append(cmd)
     out.append("| kernel | launches | total ns | avg ns | share |\n|---|---|---|---|---|")
     for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
         out.append("| `%s` | %d | %.0f | %.0f | %.1f%% |" % (k, len(v), sum(v), sum(v) / len(v), 100 * sum(v) / tot))
@@ -80,12 +81,16 @@ for f in ("bench.json", "bench_ref.json"):
     if os.path.isfile(p) and os.path.getsize(p):
         out.append("## %s\n\n```json\n%s```\n" % (f, open(p).read()))
 launches()
+launches("launches_timed_region.csv",
+         "## ncu launch list of the TIMED REGION only (cudaProfilerStart/Stop around the K steps; ns per launch)\n",
+         "command: ncu --profile-from-start off ... python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 "
+         "--profile-timed-region (every launch between the two CUDA events that bracket the K timed steps)\n")
 traffic = full("prof_step")
 open(os.path.join("profiles", tag + "_summary.md"), "w").write("\n".join(out))
 if traffic:
     json.dump({"k_step_8_bytes_per_launch": traffic, "source": "profiles/%s_summary.md (ncu --set full, dram__bytes_read+write)" % tag,
                "envs_per_launch": 1 << 20}, open("profiles/traffic.json", "w"))
-for f in ("launches.csv",):
+for f in ("launches.csv", "launches_timed_region.csv"):
     p = os.path.join(src, f)
     if os.path.isfile(p):
         open(os.path.join("profiles", tag + "_" + f), "w").write(open(p).read())
