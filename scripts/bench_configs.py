@@ -83,6 +83,76 @@ def config_ppo_feed(quick):
          achieved_gbs=1167 * B / dt / 1e9)
 
 
+def reference_shaped_net(S):
+    """Random-init network with the layer shapes of the reference's CNNBase + actor / critic heads
+    (a2c_ppo_acktr/model.py:288-305) for a (4,S,S) input; the caller's dense NN, plain torch, fp32."""
+    import torch.nn as nn
+    body = nn.Sequential(nn.Conv2d(4, 32, 3, stride=2, padding=1), nn.ReLU(), nn.Conv2d(32, 64, 2), nn.ReLU(),
+                         nn.Conv2d(64, 64, 2), nn.ReLU(), nn.Flatten())
+    with torch.no_grad():
+        feat = body(torch.zeros(1, 4, S, S)).shape[1]
+    trunk = nn.Sequential(body, nn.Linear(feat, 512), nn.ReLU())
+    return trunk.cuda(), nn.Linear(512, S * S).cuda(), nn.Linear(512, 1).cuda()
+
+
+def config_ppo_rollout(quick):
+    """configs[3] end to end: network forward -> legal-move-restricted sampling (oth_masked_categorical) -> env step,
+    (a) as a plain lockstep rollout on VecOthelloEnv, (b) through the self-play protocol PPOEnvs.step."""
+    from gymothelloenv_b200 import LegalMoveSampler, PPOEnvs
+    B, S = 65536, 8
+    torch.manual_seed(0)
+    trunk, actor, critic = reference_shaped_net(S)
+    env = VecOthelloEnv(B, board_size=S, seed=0, auto_reset=True, obs_layout="planes4", obs_dtype=torch.float32)
+    stagger(env, 20)
+    sampler = LegalMoveSampler(env)
+
+    @torch.no_grad()
+    def net_only():
+        h = trunk(env.obs)
+        return actor(h), critic(h)
+
+    @torch.no_grad()
+    def rollout_step():
+        logits, value = net_only()
+        a, lp = sampler.sample(logits)
+        env.step(a)
+    reps = 50 if quick else 300
+    dt_net = timed(net_only, reps)
+    dt_all = timed(rollout_step, reps)
+    emit(config="ppo_rollout_lockstep", envs=B, net="CNNBase-shaped (conv 4-32-64-64, fc 512) + actor/critic heads, fp32 torch",
+         ms_net_forward=dt_net * 1e3, ms_net_sample_step=dt_all * 1e3, ms_sampler_plus_env=(dt_all - dt_net) * 1e3,
+         rollout_steps_per_s=B / dt_all)
+
+    class Pol(object):
+        sampler = None
+
+        @torch.no_grad()
+        def act(self, obs, hxs, masks, choices):
+            h = trunk(obs)
+            a, lp = self.sampler.sample(actor(h))
+            return critic(h).squeeze(1), a.unsqueeze(1), lp, torch.zeros_like(lp)
+    pol = Pol()
+    envs = PPOEnvs(B, None, pol, "cuda:0", board_size=S, num_disk_as_reward=True, seed=3)
+    pol.sampler = LegalMoveSampler(envs.vec)
+    games = 1 if quick else 3
+    tuples = calls = acts = 0
+    torch.cuda.synchronize()
+    t0 = time.time()
+    for g in range(games):
+        envs.reset()
+        while True:
+            obs, actions, rewards, dones, infos, outputs, masks, bad = envs.step(None)
+            calls += 1
+            acts += envs.policy_calls
+            tuples += int((infos.type == 0).sum())
+            if bool(dones.all()):
+                break
+    torch.cuda.synchronize()
+    dt = time.time() - t0
+    emit(config="ppo_selfplay_protocol", envs=B, games_per_env=games, step_calls=calls, seconds=dt,
+         learning_tuples_per_s=tuples / dt, tuples=tuples, ms_per_step_call=dt / calls * 1e3)
+
+
 def config_tournaments(quick):
     """configs[0] and [2]: fused rollouts, README protocol (<= 10 random opening plies, fixed colours)."""
     cases = [("rand", "rand", 1 << 22), ("rand", "greedy", 1 << 22), ("greedy", "rand", 1 << 22),
@@ -114,6 +184,8 @@ if __name__ == "__main__":
         config_board_sizes(args.quick)
     if args.only in ("", "ppo"):
         config_ppo_feed(args.quick)
+    if args.only in ("", "ppo", "ppo_rollout"):
+        config_ppo_rollout(args.quick)
     if args.only in ("", "tournament"):
         config_tournaments(args.quick)
     emit(config="done", wall_s=time.time() - t0)
