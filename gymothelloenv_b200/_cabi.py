@@ -21,6 +21,7 @@ F_LEGACY_SINGLE_MOVE_PLANE = 0x08
 F_ZERO_IF_TERMINATED = 0x10
 F_SP_FRESH_STATE = 0x20
 F_SEARCH_SMALL_LISTS = 0x40
+F_SEARCH_PER_THREAD = 0x80
 
 # self-play phase bits (OTH_SP_*) and categorical modes (OTH_CAT_*)
 SP_PENDING, SP_EMITTED, SP_FINISHED, SP_PREV_P = 0x01, 0x02, 0x04, 0x08

@@ -34,8 +34,11 @@ def _nvcc():
 
 
 def _sources():
-    names = ["oth_core.cuh", "oth_kernels.cuh", "oth_size.cu", "oth_cabi.cu"]
-    return [os.path.join(CSRC, n) for n in names] + [os.path.join(INCLUDE, "othello_b200.h")]
+    """Every file the library is compiled from: all of csrc/ and include/ (a fixed list once missed a new
+    header, so edits to it did not trigger a rebuild)."""
+    files = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n.endswith((".cu", ".cuh", ".h"))]
+    files += [os.path.join(INCLUDE, n) for n in sorted(os.listdir(INCLUDE)) if n.endswith(".h")]
+    return files
 
 
 def source_digest():

@@ -13,8 +13,9 @@
 // Values only travel upwards through min / max, so the result does not depend on the order of evaluation;
 // the one place where ties matter is the root (np.argmax first occurrence, :151-155), reduced with
 // (value, lowest index).  Depth 4 = the root's moves in sequence, each searched to depth 3 cooperatively.
-// Capacity overflow (more than COOP_CAP1 root moves or COOP_CAP2 pairs) falls back to the per-thread DFS;
-// OTH_F_SEARCH_SMALL_LISTS shrinks both limits so that the tests run that fallback constantly.
+// More (root move, reply) pairs than list 2 holds: the root moves are processed in batches that fit.  More than
+// COOP_CAP1 root moves (never seen on 8x8): that decision falls back to the per-thread DFS;
+// OTH_F_SEARCH_SMALL_LISTS shrinks both limits so that the tests run the batching and the fallback constantly.
 #pragma once
 #include "oth_core.cuh"
 
@@ -34,7 +35,7 @@ struct CoopLevel2 {
 };
 // per warp: either one 32-lane group with both lists (depth >= 3) or 32 / COOP_GW2 narrow groups with list 1 only
 #ifndef COOP_GW2
-#define COOP_GW2 8          // lanes per game for depth 2 (4 measured within noise of 8: 2.91e7 vs 2.87e7 games/s)
+#define COOP_GW2 8          // lanes per game for depth 2 (4: rollouts +0.6 %, batched policy -4 %; profiles/r01p_policy.md)
 #endif
 union CoopScratch {
     struct { CoopLevel1 l1; CoopLevel2 l2; } wide;
@@ -74,16 +75,19 @@ OTH_DEV u64 coop_drop_lowest(u64 m, int k) {
 // list (dpl/dop/dmv/dval/dfirst): child q = the q-th (parent, move) pair in (parent, ascending move) order.
 // child_is_me: the side to move at the children is the searching side.  Returns the total number of moves of all
 // children (the next level's item count).
+// The parents may be a BATCH of a longer list: sfirst keeps the list's absolute item numbering and item_base is the
+// absolute number of the batch's first item (= sfirst[0]); children are stored from index 0.
 template <int S, int GW>
 OTH_DEV int coop_expand(const u64 *spl, const u64 *sop, const u64 *smv, const short *sfirst, int n_src, int n_items,
-                        u64 *dpl, u64 *dop, u64 *dmv, int *dval, short *dfirst, bool child_is_me, int gl, u32 gmask) {
+                        int item_base, u64 *dpl, u64 *dop, u64 *dmv, int *dval, short *dfirst, bool child_is_me, int gl,
+                        u32 gmask) {
     const int chunk = (n_items + GW - 1) / GW;
     const int q0 = min(gl * chunk, n_items), q1 = min(q0 + chunk, n_items);
     int local = 0;
     if (q0 < q1) {
-        int p = coop_find_node(sfirst, n_src, q0);
+        int p = coop_find_node(sfirst, n_src, q0 + item_base);
         u64 pl = spl[p], op = sop[p];
-        u64 m = coop_drop_lowest(smv[p], q0 - sfirst[p]);
+        u64 m = coop_drop_lowest(smv[p], q0 + item_base - sfirst[p]);
         for (int q = q0; q < q1; q++) {
             while (m == 0ull) { p++; pl = spl[p]; op = sop[p]; m = smv[p]; }
             const u64 mv = m & (0ull - m);
@@ -173,21 +177,33 @@ OTH_DEV int coop_search(u64 P, u64 O, u64 M, bool top_is_me, CoopLevel1 &l1, Coo
     if constexpr (DEPTH == 2) {
         coop_leaves<S, GW>(l1.pl, l1.op, l1.mv, l1.val, l1.first, n1, n2, !top_is_me, gl, gmask);
     } else {
-        ok = n2 <= cap2;                                             // group-uniform
-        if (!ok) return 0;
-        const int n3 = coop_expand<S, GW>(l1.pl, l1.op, l1.mv, l1.first, n1, n2, l2->pl, l2->op, l2->mv, l2->val,
-                                          l2->first, top_is_me, gl, gmask);
-        coop_leaves<S, GW>(l2->pl, l2->op, l2->mv, l2->val, l2->first, n2, n3, top_is_me, gl, gmask);
-        // fold list 2 into list 1: the side to move at a level-1 node is the other side
-        for (int j = gl; j < n1; j += GW) {
-            const int a = l1.first[j], b = l1.first[j + 1];
-            if (a < b) {
-                int v = top_is_me ? COOP_INF : -1;
-                for (int p = a; p < b; p++) v = top_is_me ? min(v, l2->val[p]) : max(v, l2->val[p]);
-                l1.val[j] = v;
+        // list 2 holds cap2 pairs: level-1 nodes are taken in batches [j0, j1) of consecutive root moves whose
+        // replies fit (one node has at most 64 replies, so with the real capacity a batch is never empty)
+        int j0 = 0;
+        while (j0 < n1) {                                            // group-uniform
+            const int base = l1.first[j0];
+            int j1 = j0 + 1;
+            while (j1 < n1 && l1.first[j1 + 1] - base <= cap2) j1++;
+            const int items = l1.first[j1] - base;
+            ok = items <= cap2;                                      // only the shrunken test capacity can fail here
+            if (!ok) return 0;
+            if (items > 0) {
+                const int n3 = coop_expand<S, GW>(l1.pl + j0, l1.op + j0, l1.mv + j0, l1.first + j0, j1 - j0, items, base,
+                                                  l2->pl, l2->op, l2->mv, l2->val, l2->first, top_is_me, gl, gmask);
+                coop_leaves<S, GW>(l2->pl, l2->op, l2->mv, l2->val, l2->first, items, n3, top_is_me, gl, gmask);
+                // fold list 2 into list 1: the side to move at a level-1 node is the other side
+                for (int j = j0 + gl; j < j1; j += GW) {
+                    const int a = l1.first[j] - base, b = l1.first[j + 1] - base;
+                    if (a < b) {
+                        int v = top_is_me ? COOP_INF : -1;
+                        for (int p = a; p < b; p++) v = top_is_me ? min(v, l2->val[p]) : max(v, l2->val[p]);
+                        l1.val[j] = v;
+                    }
+                }
+                __syncwarp(gmask);
             }
+            j0 = j1;
         }
-        __syncwarp(gmask);
     }
     // top: max (min) over the root moves, first occurrence on ties
     int bv = top_is_me ? -1 : COOP_INF, bi = 0x7FFF;

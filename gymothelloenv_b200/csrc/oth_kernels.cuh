@@ -911,6 +911,29 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_policy(oth_state s, i64 B, int ki
     actions_out[i] = a;
 }
 
+// batched maximin (depth >= 2) on single-word boards: the warp stays convergent and searches its 32 positions
+// lane-cooperatively (oth_coop_search.cuh) instead of 32 divergent per-thread DFS walks
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_policy_coop(oth_state s, i64 B, int depth, i64 *actions_out) {
+    static_assert(Geo<S>::W == 1, "cooperative search: single-word boards");
+    __shared__ CoopScratch coop[OTH_WARPS];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    EnvRegs<S> e = empty_env<S>();
+    bool need = false;
+    if (i < B) {
+        load_env<S>(e, s, i, B);
+        need = !(e.meta & OTH_META_TERMINATED) && any(e.legal);
+    }
+    const bool wm = e.meta & OTH_META_TURN_WHITE;
+    const u64 own = wm ? e.white.w[0] : e.black.w[0], opp = wm ? e.black.w[0] : e.white.w[0];
+    CoopScratch &sc = coop[threadIdx.x >> 5];
+    int a = -1;
+    if (depth == 2) a = coop_maximin_pick<S, 2>(need, own, opp, e.legal.w[0], sc, false);
+    else if (depth == 3) a = coop_maximin_pick<S, 3>(need, own, opp, e.legal.w[0], sc, false);
+    else a = coop_maximin_pick<S, 4>(need, own, opp, e.legal.w[0], sc, false);
+    if (i < B) actions_out[i] = need ? a : -1;
+}
+
 // -------------------------------------------------------------------------- rollout
 struct RolloutParams {
     i64 B;
@@ -1170,13 +1193,21 @@ struct SizeLaunch {
     }
     static cudaError_t policy(oth_state s, i64 B, int kind, int depth, u64 seed, u64 counter, i64 base, i64 *out,
                               cudaStream_t q) {
+        if constexpr (Geo<S>::W == 1) {
+            // measured on 2^18 mid-game 8x8 positions, cooperative vs per-thread DFS: depth 2 0.51 vs 0.73 ms,
+            // depth 3 4.8 vs 12.6 ms, depth 4 60 vs 202 ms (profiles/r01p_policy.md)
+            if (kind == OTH_POLICY_MAXIMIN && depth >= 2) {
+                k_policy_coop<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, depth, out);
+                return cudaGetLastError();
+            }
+        }
         k_policy<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, kind, depth, seed, counter, base, out);
         return cudaGetLastError();
     }
     static cudaError_t rollout(const RolloutParams &p, cudaStream_t q) {
         const bool searches = (p.black.kind == OTH_POLICY_MAXIMIN && p.black.depth >= 2) ||
                               (p.white.kind == OTH_POLICY_MAXIMIN && p.white.depth >= 2);
-        if (Geo<S>::W == 1 && searches) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        if (Geo<S>::W == 1 && searches && !(p.flags & OTH_F_SEARCH_PER_THREAD)) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
         else k_rollout<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
         return cudaGetLastError();
     }

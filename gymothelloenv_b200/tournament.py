@@ -31,7 +31,8 @@ def parse_policy(spec):
 
 
 def rollout(num_envs, black, white, board_size=8, initial_rand_steps=10, games_per_env=1, seed=0, env_id_base=0,
-            device=None, num_disk_as_reward=False, record=False, trace_len=0, tally=None, search_small_lists=False):
+            device=None, num_disk_as_reward=False, record=False, trace_len=0, tally=None, search_small_lists=False,
+            search_per_thread=False):
     """Launches oth_rollout for `num_envs` threads x `games_per_env` games on this device.
 
     Returns (tally int64[4] CUDA tensor = black wins, draws, white wins, plies, records)
@@ -58,6 +59,8 @@ def rollout(num_envs, black, white, board_size=8, initial_rand_steps=10, games_p
     flags = _cabi.F_SUDDEN_DEATH | (_cabi.F_DISK_REWARD if num_disk_as_reward else 0)
     if search_small_lists:                        # tests: force the cooperative search onto its per-thread fallback
         flags |= _cabi.F_SEARCH_SMALL_LISTS
+    if search_per_thread:                         # A/B: per-thread DFS instead of the lane-cooperative search
+        flags |= _cabi.F_SEARCH_PER_THREAD
     with torch.cuda.device(dev):
         _cabi.check(lib.oth_rollout(int(num_envs), int(board_size), flags, policy_spec(bk, bd), policy_spec(wk, wd),
                                     int(initial_rand_steps), int(games_per_env), int(seed) & 0xFFFFFFFFFFFFFFFF,

@@ -67,6 +67,8 @@ typedef struct oth_state {
                                          (the worker's `o`, ppo_run_self_play.py:246,274); legal_mask unaffected */
 #define OTH_F_SP_FRESH_STATE 0x20     /* oth_selfplay_advance: refresh the saved state on EVERY protagonist ply
                                          (default: keep ppo_run_self_play.py:291-301's stale state in pass runs) */
+#define OTH_F_SEARCH_PER_THREAD 0x80   /* oth_rollout: every maximin decision by the per-thread DFS (no lane-cooperative
+                                           search); same results, for A/B timing and cross-checks */
 #define OTH_F_SEARCH_SMALL_LISTS 0x40  /* oth_rollout, tests only: the lane-cooperative maximin search keeps at most 3 root
                                            moves / 12 (move, reply) pairs, so its per-thread fallback runs constantly */
 

@@ -42,7 +42,7 @@ def test_header_constants_match_python_binding():
     defs = {k: int(v.rstrip("u"), 0) for k, v in re.findall(r"#define\s+(OTH_[A-Z0-9_]+)\s+(0x[0-9a-fA-F]+u?|\d+)\b", header)}
     pairs = {"OTH_F_SUDDEN_DEATH": _cabi.F_SUDDEN_DEATH, "OTH_F_DISK_REWARD": _cabi.F_DISK_REWARD,
              "OTH_F_AUTO_RESET": _cabi.F_AUTO_RESET, "OTH_F_LEGACY_SINGLE_MOVE_PLANE": _cabi.F_LEGACY_SINGLE_MOVE_PLANE,
-             "OTH_F_SEARCH_SMALL_LISTS": _cabi.F_SEARCH_SMALL_LISTS, "OTH_F_SP_FRESH_STATE": _cabi.F_SP_FRESH_STATE,
+             "OTH_F_SEARCH_SMALL_LISTS": _cabi.F_SEARCH_SMALL_LISTS, "OTH_F_SEARCH_PER_THREAD": _cabi.F_SEARCH_PER_THREAD, "OTH_F_SP_FRESH_STATE": _cabi.F_SP_FRESH_STATE,
              "OTH_OBS_BOARD": _cabi.OBS_BOARD, "OTH_OBS_BOARD_MASK": _cabi.OBS_BOARD_MASK,
              "OTH_OBS_PLANES4": _cabi.OBS_PLANES4, "OTH_OBS_PLANES3": _cabi.OBS_PLANES3,
              "OTH_OBS_ABSOLUTE": _cabi.OBS_ABSOLUTE, "OTH_DTYPE_F32": _cabi.DTYPE_F32,
@@ -163,3 +163,13 @@ def test_sharded_tally_over_gloo_world_size_2(tmp_path):
     res = (ids * 2654435761 >> 7) % 3
     want = [(res == 0).sum(), (res == 1).sum(), (res == 2).sum(), (ids % 61 + 40).sum()]
     assert got.tolist() == [int(x) for x in want]
+
+
+def test_build_digest_covers_every_native_source():
+    """A source file outside the digest makes `build()` keep a stale library after an edit."""
+    from gymothelloenv_b200 import build
+    hashed = {os.path.abspath(p) for p in build._sources()}
+    csrc = os.path.join(ROOT, "gymothelloenv_b200", "csrc")
+    for n in os.listdir(csrc):
+        assert os.path.abspath(os.path.join(csrc, n)) in hashed, n
+    assert os.path.abspath(os.path.join(ROOT, "include", "othello_b200.h")) in hashed
