@@ -104,6 +104,19 @@ def test_cooperative_search_fallback_rederived_on_host(S, black, white, init_ran
     _check_rollout(S, black, white, init_rand, games, search_small_lists=True)
 
 
+@pytest.mark.parametrize("black,white,games", [("greedy", "maximin2", 4099), ("maximin3", "rand", 1500),
+                                               ("maximin4", "maximin2", 200), ("maximin3", "maximin3", 777)])
+def test_cooperative_and_per_thread_search_play_identical_games(black, white, games):
+    """OTH_F_SEARCH_PER_THREAD: the per-thread DFS and the lane-cooperative search are two implementations of
+    MaxiMinPolicy.search; every recorded game (result, plies, final counts, action trace) must coincide."""
+    kw = dict(board_size=8, initial_rand_steps=10, seed=99, env_id_base=123456789, record=True, trace_len=72)
+    ta, ra = _rollout(games, black, white, **kw)
+    tb, rb = _rollout(games, black, white, search_per_thread=True, **kw)
+    assert ta.tolist() == tb.tolist()
+    for k in ("result", "plies", "counts", "trace"):
+        assert torch.equal(ra[k], rb[k]), k
+
+
 def test_sharding_invariance_and_multi_game_envs():
     """Global env ids key the RNG: any split of the id range plays the same games."""
     S, seed = 8, 99
