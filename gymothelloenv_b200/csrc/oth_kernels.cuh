@@ -22,7 +22,10 @@ enum { ROW_BLACK = 0, ROW_WHITE = 1, ROW_LEGAL = 2, ROW_ZERO = 3, ROW_ONES = 4, 
 enum { NIB_POS0 = 0, NIB_POS1 = 1, NIB_POS2 = 2, NIB_POS3 = 3, NIB_NEG0 = 4, NIB_MASK = 5, NIB_ROWS = 6 };
 template <int S, bool NIB = ((S * S) % 4 == 0)>
 struct WarpStageT {
-    u64 row[ROW_COUNT][Geo<S>::W][32];
+    union {
+        u64 row[ROW_COUNT][Geo<S>::W][32];
+        uint4 slab[(32 * S * S + 15) / 16];               // odd-size slab writer (int8 outputs): 32 envs x S*S bytes
+    };
 };
 template <int S>
 struct WarpStageT<S, true> {
@@ -368,6 +371,104 @@ OTH_DEV void slab_expand(unsigned char *slab, int lane, const BB<Geo<S>::W> &pos
         dst[r] = w;
     }
 }
+// Odd sizes (S*S % 4 != 0): lane e's S*S bytes start at byte e*S*S of the slab, `a` = that offset mod 4 past an
+// aligned word.  The lane shifts its bitboards up by a, so aligned word j holds its cells 4j-a .. 4j-a+3 and the
+// nibble extraction keeps compile-time shifts; words 1 .. N/4-1 are always wholly its own (one 32-bit store each),
+// the first word and the last two may be shared with the neighbouring envs and are stored byte by byte.
+template <int W> OTH_DEV BB<W> bb_shl_small(const BB<W> &x, int a) {     // 0 <= a <= 3
+    BB<W> r;
+    BB_FOR(i) {
+        const u64 lo = i > 0 ? x.w[i > 0 ? i - 1 : 0] : 0ull;
+        r.w[i] = (x.w[i] << a) | ((lo >> 1) >> (63 - a));
+    }
+    return r;
+}
+template <int S, bool HAS_NEG>
+OTH_DEV void slab_expand_odd(unsigned char *slab, int lane, const BB<Geo<S>::W> &pos, const BB<Geo<S>::W> &neg) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, JF = N / 4;
+    static_assert(N % 4 != 0 && N + 3 <= 64 * W, "odd board sizes whose shifted board still fits its words");
+    const int start = lane * N, a = start & 3;
+    const BB<W> ps = bb_shl_small<W>(pos, a), ns = bb_shl_small<W>(neg, a);
+    unsigned char *base = slab + (start - a);
+    u32 *dst = reinterpret_cast<u32 *>(base);
+#pragma unroll
+    for (int j = 0; j <= JF + 1; j++) {
+        if (4 * j >= 64 * W) continue;
+        const int k = j >> 4, sh = 4 * (j & 7);
+        const bool hi = (j & 8) != 0;
+        const u32 ph = hi ? (u32)(ps.w[k] >> 32) : (u32)ps.w[k];
+        u32 w = spread4((ph >> sh) & 0xFu);
+        if constexpr (HAS_NEG) {
+            const u32 nh = hi ? (u32)(ns.w[k] >> 32) : (u32)ns.w[k];
+            w = spread4((nh >> sh) & 0xFu) * 0xFFu + w;
+        }
+        if (j >= 1 && j < JF) {
+            dst[j] = w;
+        } else {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int c = 4 * j + b - a;                         // cell index of byte b of word j
+                if (c >= 0 && c < N) base[4 * j + b] = (unsigned char)(w >> (8 * b));
+            }
+        }
+    }
+}
+// float32 observations of odd sizes, full warp: no staging.  A cell is 4 bytes, so every (env, plane) row of S*S
+// floats is 4-byte aligned; for env e = 0..31 and each plane, the owner lane's bitboard is broadcast by shuffle
+// and lane l writes cells l, l+32, ...: one store instruction = 32 consecutive floats = 128 contiguous bytes.
+// Cell l + 32*i is bit l of 32-bit half i of the board, so the half is picked at compile time.
+template <int S, int LAYOUT>
+OTH_DEV void rows_write_f32(void *base, i64 env0, int lane, const BB<Geo<S>::W> &black, const BB<Geo<S>::W> &white,
+                            const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, P = layout_planes(LAYOUT);
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    const BB<W> zero = bb_zero<W>();
+    BB<W> pos[P], neg = zero;
+    if constexpr (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK) {   // othello.py:363-376
+        pos[0] = bb_select(tw, white, black); neg = bb_select(tw, black, white);
+        if constexpr (LAYOUT == OTH_OBS_BOARD_MASK) pos[1] = lg;
+    } else if constexpr (LAYOUT == OTH_OBS_ABSOLUTE) {
+        pos[0] = white; neg = black;
+    } else {                                                                   // util.py:48-74, run_2agent.py:29-46
+        pos[0] = black; pos[1] = white;
+        pos[2] = bb_select(tw, geo_full<S>(), zero);
+        if constexpr (LAYOUT == OTH_OBS_PLANES4) pos[3] = bb_select(quirk_empty, zero, lg);
+    }
+    u32 *out = reinterpret_cast<u32 *>(base) + env0 * (i64)(P * N);
+#pragma unroll 2
+    for (int e = 0; e < 32; e++) {
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+            u32 *row = out + (e * P + p) * N;
+#pragma unroll
+            for (int i = 0; i < (N + 31) / 32; i++) {
+                const u64 pw = __shfl_sync(0xFFFFFFFFu, pos[p].w[i >> 1], e);
+                const u32 ph = (i & 1) ? (u32)(pw >> 32) : (u32)pw;
+                u32 v = ((ph >> lane) & 1u) * 0x3F800000u;
+                if (HAS_NEG && p == 0) {
+                    const u64 nw = __shfl_sync(0xFFFFFFFFu, neg.w[i >> 1], e);
+                    const u32 nh = (i & 1) ? (u32)(nw >> 32) : (u32)nw;
+                    v |= ((nh >> lane) & 1u) * 0xBF800000u;
+                }
+                const int c = lane + 32 * i;
+                if (32 * i + 32 <= N || c < N) row[c] = v;
+            }
+        }
+    }
+}
+template <int S>
+OTH_DEV void rows_write_f32_layout(int layout, void *base, i64 env0, int lane, const BB<Geo<S>::W> &black,
+                                   const BB<Geo<S>::W> &white, const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
+    switch (layout) {
+    case OTH_OBS_BOARD: rows_write_f32<S, OTH_OBS_BOARD>(base, env0, lane, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_BOARD_MASK: rows_write_f32<S, OTH_OBS_BOARD_MASK>(base, env0, lane, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_PLANES4: rows_write_f32<S, OTH_OBS_PLANES4>(base, env0, lane, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_PLANES3: rows_write_f32<S, OTH_OBS_PLANES3>(base, env0, lane, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_ABSOLUTE: rows_write_f32<S, OTH_OBS_ABSOLUTE>(base, env0, lane, black, white, lg, tw, quirk_empty); break;
+    default: break;
+    }
+}
+
 template <int S>
 OTH_DEV void slab_copy(const unsigned char *slab, void *base, i64 env0, int lane) {
     constexpr int N = Geo<S>::N, CH = 2 * N;                       // 32*N bytes = 2N chunks of 16
@@ -466,6 +567,36 @@ OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, bool ze
     } else {
         constexpr int W = Geo<S>::W;
         const int lane = threadIdx.x & 31;
+        {
+            const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
+            const bool obs_slab = layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
+            const bool obs_rows = layout != OTH_OBS_NONE && out.obs_dtype == OTH_DTYPE_F32;
+            if (warp_env0 + 32 <= B && (obs_slab || obs_rows || layout == OTH_OBS_NONE)) {   // warp-uniform, full warp
+                const bool live = active && !zero_obs, tw = live && (e.meta & OTH_META_TURN_WHITE);
+                const BB<W> zero = bb_zero<W>();
+                const BB<W> black = bb_select(live, e.black, zero), white = bb_select(live, e.white, zero);
+                const BB<W> lg_mask = bb_select(active && !zero_mask, e.legal, zero);
+                unsigned char *slab = reinterpret_cast<unsigned char *>(&st.slab[0]);
+                if (obs_rows) {
+                    const BB<W> lg = bb_select(live, e.legal, zero);
+                    const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(lg) <= 1;   // util.py:55
+                    rows_write_f32_layout<S>(layout, out.obs, warp_env0, lane, black, white, lg, tw, quirk);
+                }
+                if (obs_slab) {                                                  // othello.py:363-369
+                    slab_expand_odd<S, true>(slab, lane, bb_select(tw, white, black), bb_select(tw, black, white));
+                    __syncwarp();
+                    slab_copy<S>(slab, out.obs, warp_env0, lane);
+                    __syncwarp();
+                }
+                if (out.legal_mask != nullptr) {
+                    slab_expand_odd<S, false>(slab, lane, lg_mask, lg_mask);
+                    __syncwarp();
+                    slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
+                    __syncwarp();
+                }
+                return;
+            }
+        }
         BB_FOR(i) {
             st.row[ROW_BLACK][i][lane] = active ? e.black.w[i] : 0ull;
             st.row[ROW_WHITE][i][lane] = active ? e.white.w[i] : 0ull;

@@ -157,7 +157,7 @@ def test_random_streams_vs_oracle(S, sudden, disk, p_invalid):
     assert steps > B * (N - 10) * (0.5 if p_invalid else 0.9) or sudden
 
 
-@pytest.mark.parametrize("S", [6, 8, 10])
+@pytest.mark.parametrize("S", [6, 8, 10, 5, 7, 9, 11, 12, 4])
 def test_auto_reset_and_all_layouts(S):
     """auto_reset: the terminal transition reports reward/done/winner, the state restarts
     in the same call; every obs layout x dtype equals the oracle's observation."""
