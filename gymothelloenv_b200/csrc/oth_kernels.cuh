@@ -413,17 +413,13 @@ OTH_DEV void slab_expand_odd(unsigned char *slab, int lane, const BB<Geo<S>::W> 
         }
     }
 }
-// float32 observations of odd sizes, full warp: no staging.  A cell is 4 bytes, so every (env, plane) row of S*S
-// floats is 4-byte aligned; for env e = 0..31 and each plane, the owner lane's bitboard is broadcast by shuffle
-// and lane l writes cells l, l+32, ...: one store instruction = 32 consecutive floats = 128 contiguous bytes.
-// Cell l + 32*i is bit l of 32-bit half i of the board, so the half is picked at compile time.
+// which bitboard gives the +1 cells of each plane of a layout, and the -1 cells of plane 0
 template <int S, int LAYOUT>
-OTH_DEV void rows_write_f32(void *base, i64 env0, int lane, const BB<Geo<S>::W> &black, const BB<Geo<S>::W> &white,
+OTH_DEV void layout_sources(BB<Geo<S>::W> *pos, BB<Geo<S>::W> &neg, const BB<Geo<S>::W> &black, const BB<Geo<S>::W> &white,
                             const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
-    constexpr int N = Geo<S>::N, W = Geo<S>::W, P = layout_planes(LAYOUT);
-    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    constexpr int W = Geo<S>::W;
     const BB<W> zero = bb_zero<W>();
-    BB<W> pos[P], neg = zero;
+    neg = zero;
     if constexpr (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK) {   // othello.py:363-376
         pos[0] = bb_select(tw, white, black); neg = bb_select(tw, black, white);
         if constexpr (LAYOUT == OTH_OBS_BOARD_MASK) pos[1] = lg;
@@ -434,6 +430,19 @@ OTH_DEV void rows_write_f32(void *base, i64 env0, int lane, const BB<Geo<S>::W> 
         pos[2] = bb_select(tw, geo_full<S>(), zero);
         if constexpr (LAYOUT == OTH_OBS_PLANES4) pos[3] = bb_select(quirk_empty, zero, lg);
     }
+}
+
+// float32 observations of odd sizes, full warp: no staging.  A cell is 4 bytes, so every (env, plane) row of S*S
+// floats is 4-byte aligned; for env e = 0..31 and each plane, the owner lane's bitboard is broadcast by shuffle
+// and lane l writes cells l, l+32, ...: one store instruction = 32 consecutive floats = 128 contiguous bytes.
+// Cell l + 32*i is bit l of 32-bit half i of the board, so the half is picked at compile time.
+template <int S, int LAYOUT>
+OTH_DEV void rows_write_f32(void *base, i64 env0, int lane, const BB<Geo<S>::W> &black, const BB<Geo<S>::W> &white,
+                            const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, P = layout_planes(LAYOUT);
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    BB<W> pos[P], neg;
+    layout_sources<S, LAYOUT>(pos, neg, black, white, lg, tw, quirk_empty);
     u32 *out = reinterpret_cast<u32 *>(base) + env0 * (i64)(P * N);
 #pragma unroll 2
     for (int e = 0; e < 32; e++) {
@@ -481,6 +490,53 @@ OTH_DEV void slab_copy(const unsigned char *slab, void *base, i64 env0, int lane
     }
 }
 
+// int8 observations of any layout, any size but 8, full warp: the flat output [env][plane][cell] is a sequence of
+// 32*P rows of S*S bytes; pass k handles rows 32k .. 32k+31: lane l fetches the bitboards of row 32k+l (env r/P,
+// plane r%P) from their owner lane by shuffle, expands them into the slab at byte l*S*S (the alignment phase of the
+// row's global offset equals that of l*S*S because 32*k*S*S is a multiple of 4), and the warp copies the slab out.
+template <int S, int LAYOUT>
+OTH_DEV void rows_i8_write(void *base, i64 env0, int lane, unsigned char *slab, const BB<Geo<S>::W> &black,
+                           const BB<Geo<S>::W> &white, const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, P = layout_planes(LAYOUT);
+    constexpr bool HAS_NEG = (LAYOUT == OTH_OBS_BOARD || LAYOUT == OTH_OBS_BOARD_MASK || LAYOUT == OTH_OBS_ABSOLUTE);
+    BB<W> pos[P], neg;
+    layout_sources<S, LAYOUT>(pos, neg, black, white, lg, tw, quirk_empty);
+    char *out = reinterpret_cast<char *>(base) + env0 * (i64)(P * N);
+#pragma unroll
+    for (int k = 0; k < P; k++) {
+        const int r = 32 * k + lane, e = r / P, p = r - e * P;
+        BB<W> sp = bb_zero<W>(), sn = bb_zero<W>();
+#pragma unroll
+        for (int q = 0; q < P; q++) {
+            BB<W> t;
+            BB_FOR(i) t.w[i] = __shfl_sync(0xFFFFFFFFu, pos[q].w[i], e);
+            if (P == 1 || p == q) sp = t;
+        }
+        if constexpr (HAS_NEG) {
+            BB<W> t;
+            BB_FOR(i) t.w[i] = __shfl_sync(0xFFFFFFFFu, neg.w[i], e);
+            if (p == 0) sn = t;
+        }
+        if constexpr (N % 4 == 0) slab_expand<S, HAS_NEG>(slab, lane, sp, sn);
+        else slab_expand_odd<S, HAS_NEG>(slab, lane, sp, sn);
+        __syncwarp();
+        slab_copy<S>(slab, out + (i64)k * 32 * N, 0, lane);
+        __syncwarp();
+    }
+}
+template <int S>
+OTH_DEV void rows_i8_write_layout(int layout, void *base, i64 env0, int lane, unsigned char *slab, const BB<Geo<S>::W> &black,
+                                  const BB<Geo<S>::W> &white, const BB<Geo<S>::W> &lg, bool tw, bool quirk_empty) {
+    switch (layout) {
+    case OTH_OBS_BOARD: rows_i8_write<S, OTH_OBS_BOARD>(base, env0, lane, slab, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_BOARD_MASK: rows_i8_write<S, OTH_OBS_BOARD_MASK>(base, env0, lane, slab, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_PLANES4: rows_i8_write<S, OTH_OBS_PLANES4>(base, env0, lane, slab, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_PLANES3: rows_i8_write<S, OTH_OBS_PLANES3>(base, env0, lane, slab, black, white, lg, tw, quirk_empty); break;
+    case OTH_OBS_ABSOLUTE: rows_i8_write<S, OTH_OBS_ABSOLUTE>(base, env0, lane, slab, black, white, lg, tw, quirk_empty); break;
+    default: break;
+    }
+}
+
 template <int W>
 OTH_DEV void stage_nibbles(uint4 *dst, const BB<W> &x) {
     BB_FOR(k) dst[k] = nibble_bytes(x.w[k]);
@@ -501,9 +557,14 @@ OTH_DEV void emit_dense_nib(const EnvRegs<S> &e, bool active, bool zero_obs, boo
     const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
     if constexpr (S != 8) {
         const bool obs_slab = layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
-        if (warp_env0 + 32 <= B && (obs_slab || layout == OTH_OBS_NONE)) {   // warp-uniform
+        const bool obs_rows8 = layout != OTH_OBS_NONE && layout != OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
+        if (warp_env0 + 32 <= B && (obs_slab || obs_rows8 || layout == OTH_OBS_NONE)) {   // warp-uniform
             static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
             unsigned char *slab = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
+            if (obs_rows8) {                                                 // multi-plane int8 layouts, row passes
+                const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(lg) <= 1;   // util.py:55
+                rows_i8_write_layout<S>(layout, out.obs, warp_env0, lane, slab, black, white, lg, live && tw, quirk);
+            }
             if (obs_slab) {                                                  // othello.py:363-369
                 slab_expand<S, true>(slab, lane, bb_select(tw, white, black), bb_select(tw, black, white));
                 __syncwarp();
@@ -571,16 +632,18 @@ OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, bool ze
             const int layout = (out.obs != nullptr) ? out.obs_layout : OTH_OBS_NONE;
             const bool obs_slab = layout == OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
             const bool obs_rows = layout != OTH_OBS_NONE && out.obs_dtype == OTH_DTYPE_F32;
-            if (warp_env0 + 32 <= B && (obs_slab || obs_rows || layout == OTH_OBS_NONE)) {   // warp-uniform, full warp
+            const bool obs_rows8 = layout != OTH_OBS_NONE && layout != OTH_OBS_BOARD && out.obs_dtype == OTH_DTYPE_I8;
+            if (warp_env0 + 32 <= B) {                                           // warp-uniform: full warp
                 const bool live = active && !zero_obs, tw = live && (e.meta & OTH_META_TURN_WHITE);
                 const BB<W> zero = bb_zero<W>();
                 const BB<W> black = bb_select(live, e.black, zero), white = bb_select(live, e.white, zero);
                 const BB<W> lg_mask = bb_select(active && !zero_mask, e.legal, zero);
                 unsigned char *slab = reinterpret_cast<unsigned char *>(&st.slab[0]);
-                if (obs_rows) {
+                if (obs_rows || obs_rows8) {
                     const BB<W> lg = bb_select(live, e.legal, zero);
                     const bool quirk = (flags & OTH_F_LEGACY_SINGLE_MOVE_PLANE) && popc(lg) <= 1;   // util.py:55
-                    rows_write_f32_layout<S>(layout, out.obs, warp_env0, lane, black, white, lg, tw, quirk);
+                    if (obs_rows) rows_write_f32_layout<S>(layout, out.obs, warp_env0, lane, black, white, lg, tw, quirk);
+                    else rows_i8_write_layout<S>(layout, out.obs, warp_env0, lane, slab, black, white, lg, tw, quirk);
                 }
                 if (obs_slab) {                                                  // othello.py:363-369
                     slab_expand_odd<S, true>(slab, lane, bb_select(tw, white, black), bb_select(tw, black, white));
