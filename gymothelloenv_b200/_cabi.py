@@ -11,7 +11,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "_lib", "libothello_b200.so")
 
 MIN_BOARD_SIZE = 4
-MAX_BOARD_SIZE = 12
+MAX_BOARD_SIZE = 16
 
 # flags (OTH_F_*)
 F_SUDDEN_DEATH = 0x01

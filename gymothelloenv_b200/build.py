@@ -20,7 +20,7 @@ INCLUDE = os.path.join(os.path.dirname(PKG), "include")
 LIB_DIR = os.path.join(PKG, "_lib")
 OBJ_DIR = os.path.join(PKG, "_lib", "obj")
 LIB_PATH = os.path.join(LIB_DIR, "libothello_b200.so")
-BOARD_SIZES = list(range(4, 13))   # must match OTH_DECL list in oth_cabi.cu / OTH_MAX_BOARD_SIZE
+BOARD_SIZES = list(range(4, 17))   # must match OTH_DECL list in oth_cabi.cu / OTH_MAX_BOARD_SIZE
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "-diag-suppress", "177"]

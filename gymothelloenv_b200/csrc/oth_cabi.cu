@@ -9,6 +9,7 @@
 
 #define OTH_DECL(S) extern "C" const OthSizeOps *oth_size_ops_##S();
 OTH_DECL(4) OTH_DECL(5) OTH_DECL(6) OTH_DECL(7) OTH_DECL(8) OTH_DECL(9) OTH_DECL(10) OTH_DECL(11) OTH_DECL(12)
+OTH_DECL(13) OTH_DECL(14) OTH_DECL(15) OTH_DECL(16)
 
 static thread_local char g_err[256] = "";
 
@@ -33,6 +34,10 @@ static const OthSizeOps *ops_for(int S) {
     case 10: return oth_size_ops_10();
     case 11: return oth_size_ops_11();
     case 12: return oth_size_ops_12();
+    case 13: return oth_size_ops_13();
+    case 14: return oth_size_ops_14();
+    case 15: return oth_size_ops_15();
+    case 16: return oth_size_ops_16();
     default: return nullptr;
     }
 }
@@ -120,7 +125,7 @@ OTH_API int oth_policy(oth_state st, int64_t B, int board_size, oth_policy_spec 
 
 OTH_API int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec black, oth_policy_spec white,
                         int init_rand_steps, int games_per_env, uint64_t seed, int64_t env_id_base,
-                        unsigned long long *tally, int8_t *game_result, int16_t *game_plies, uint8_t *game_counts,
+                        unsigned long long *tally, int8_t *game_result, int16_t *game_plies, int16_t *game_counts,
                         int16_t *trace, int trace_stride, void *stream) {
     const OthSizeOps *ops = ops_for(board_size);
     if (ops == nullptr) return fail(OTH_ERR_BAD_BOARD_SIZE, "board_size unsupported");
@@ -279,9 +284,9 @@ OTH_API int oth_ts_advance(oth_state st, oth_teacher_student ts, int64_t B, int 
 }
 
 // ---- legal-move-restricted categorical (model.py:60-150,156-198) ---------------------
-// One warp per env; lane l holds actions l, l+32, ... (N <= 160).  float32, max-subtracted.
+// One warp per env; lane l holds actions l, l+32, ... (N <= 256).  float32, max-subtracted.
 #define OTH_STREAM_SAMPLE 3u
-constexpr int CAT_MAXK = 5;
+constexpr int CAT_MAXK = 8;    // 32 lanes x 8 cells = 256 = the largest board (16 x 16)
 __global__ void __launch_bounds__(128) k_masked_categorical(const float *logits, const u64 *legal, i64 B, int N, int mode,
                                                             const i64 *actions_in, u64 seed, u64 counter, i64 base,
                                                             i64 *actions_out, float *logp_out) {
@@ -405,10 +410,10 @@ __global__ void __launch_bounds__(128) k_epsilon_greedy(const float *q, const u6
     if (env >= B) return;
     const int K = (N + 31) >> 5, W = (N + 63) >> 6;
     const float NEG_INF = __int_as_float(0xFF800000u);
-    u64 words[3] = {0ull, 0ull, 0ull};
+    u64 words[4] = {0ull, 0ull, 0ull, 0ull};                       // W <= 4 (16 x 16)
     int n_legal = 0;
 #pragma unroll
-    for (int w = 0; w < 3; w++)
+    for (int w = 0; w < 4; w++)
         if (w < W) { words[w] = legal[(i64)w * B + env]; n_legal += __popcll(words[w]); }
     float x[CAT_MAXK];
     float best = NEG_INF;
@@ -418,7 +423,7 @@ __global__ void __launch_bounds__(128) k_epsilon_greedy(const float *q, const u6
         const int a = 32 * k + lane;
         x[k] = 0.f;
         if (k < K && a < N) {
-            const u64 word = (a >> 6) == 0 ? words[0] : ((a >> 6) == 1 ? words[1] : words[2]);
+            const u64 word = (a >> 6) == 0 ? words[0] : ((a >> 6) == 1 ? words[1] : ((a >> 6) == 2 ? words[2] : words[3]));
             const bool ok = (word >> (a & 63)) & 1ull;
             if (ok) {
                 x[k] = q[env * N + a];
@@ -445,11 +450,11 @@ __global__ void __launch_bounds__(128) k_epsilon_greedy(const float *q, const u6
             int n = bounded(r1, n_legal);                          // random.randrange(len(possible_moves))
             int wsel = 0;
 #pragma unroll
-            for (int w = 0; w < 2; w++) {
+            for (int w = 0; w < 3; w++) {
                 const int c = __popcll(words[w]);
                 if (wsel == w && n >= c) { n -= c; wsel = w + 1; }
             }
-            const u64 word = wsel == 0 ? words[0] : (wsel == 1 ? words[1] : words[2]);
+            const u64 word = wsel == 0 ? words[0] : (wsel == 1 ? words[1] : (wsel == 2 ? words[2] : words[3]));
             chosen = 64 * wsel + nth_bit64(word, n);
         } else {
             chosen = bi;

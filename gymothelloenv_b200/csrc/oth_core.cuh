@@ -179,7 +179,7 @@ OTH_DEV u64 legal1(u64 P, u64 O) {
     else return moves & ~(P | O) & GeoWord<S, 0>::full;
 }
 
-// ---- multi-word boards (S = 9..12, W = 2..3): whole-board arithmetic --------------------
+// ---- multi-word boards (S = 9..16, W = 2..4): whole-board arithmetic --------------------
 // The single-word tricks carry over once add / subtract / bit-reverse work on the whole W-word
 // board: a row is still S contiguous bits (it may straddle a word boundary, which is why the
 // carry must run through all words), and the bit-reversed board still has contiguous rows.
@@ -231,7 +231,7 @@ template <int W> OTH_DEV BB<W> carry_moves(const BB<W> &P, const BB<W> &Oi) {
     return andnot(bb_add<W>(Oi, shl<1, W>(P) & Oi), Oi);
 }
 // The three other axes: paired Kogge-Stone fills sharing the doubled propagators between the two
-// opposite directions; reach after the rounds: 2, 4, 8, 12 cells (the longest run is S-2 <= 10).
+// opposite directions; reach after the rounds: 2, 4, 8, 12, 16 cells (the longest run is S-2 <= 14).
 template <int S, int D>
 OTH_DEV BB<Geo<S>::W> pair_moves(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &m) {
     constexpr int W = Geo<S>::W;
@@ -246,6 +246,10 @@ OTH_DEV BB<Geo<S>::W> pair_moves(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &m)
         fl = fl | (pl2 & shl<4 * D, W>(fl));
         fr = fr | (pr2 & shr<4 * D, W>(fr));
         if constexpr (S - 2 > 8) {
+            fl = fl | (pl2 & shl<4 * D, W>(fl));
+            fr = fr | (pr2 & shr<4 * D, W>(fr));
+        }
+        if constexpr (S - 2 > 12) {
             fl = fl | (pl2 & shl<4 * D, W>(fl));
             fr = fr | (pr2 & shr<4 * D, W>(fr));
         }
@@ -299,8 +303,12 @@ OTH_DEV u64 ray_flips1(u64 m, u64 P, u64 O) {
     const u64 x = O | ~m;
     const u64 t = x + 1ull;
     const u64 stop = t & ~x & P;                       // 0 or the single closing own disc
+#ifdef OTH_RAY_V2
+    return stop != 0ull ? (m & O & ~t) : 0ull;         // ray cells the carry rippled through (all opponent discs)
+#else
     const u64 d = stop - (stop != 0ull ? 1ull : 0ull); // bits below the closing disc
     return d & m;
+#endif
 }
 template <int S>
 OTH_DEV u64 flips1_up(u64 mv, u64 P, u64 O, u64 Oi) {
@@ -363,8 +371,15 @@ template <int W> OTH_DEV BB<W> ray_flips(const BB<W> &m, const BB<W> &P, const B
     const BB<W> t = bb_add<W>(x, bb_one<W>(1ull));
     BB<W> stop;
     BB_FOR(i) stop.w[i] = t.w[i] & ~x.w[i] & P.w[i];       // 0 or the single closing own disc
+#ifdef OTH_RAY_V2
+    const bool closed = any(stop);
+    BB<W> r;
+    BB_FOR(i) r.w[i] = closed ? (m.w[i] & O.w[i] & ~t.w[i]) : 0ull;   // ray cells the carry rippled through
+    return r;
+#else
     const BB<W> d = bb_sub<W>(stop, bb_one<W>(any(stop) ? 1ull : 0ull));
     return d & m;
+#endif
 }
 // the four rays towards higher bit indices from cell a (mv = its bit): east needs no ray mask -- the
 // carry out of mv<<1 ripples through the inner-column opponent run and lands on the cell behind it

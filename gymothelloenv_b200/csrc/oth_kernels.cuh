@@ -1140,7 +1140,7 @@ struct RolloutParams {
     unsigned long long *tally;
     int8_t *game_result;
     int16_t *game_plies;
-    uint8_t *game_counts;
+    int16_t *game_counts;
     int16_t *trace;
     int trace_stride;
 };
@@ -1184,8 +1184,8 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
             if (p.game_result) p.game_result[game] = (int8_t)r.winner;
             if (p.game_plies) p.game_plies[game] = (int16_t)ply;
             if (p.game_counts) {
-                p.game_counts[2 * game] = (uint8_t)popc(e.black);
-                p.game_counts[2 * game + 1] = (uint8_t)popc(e.white);
+                p.game_counts[2 * game] = (int16_t)popc(e.black);
+                p.game_counts[2 * game + 1] = (int16_t)popc(e.white);
             }
         }
     }
@@ -1271,8 +1271,8 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout_coop(RolloutParams p) {
             if (p.game_result) p.game_result[game] = (int8_t)r.winner;
             if (p.game_plies) p.game_plies[game] = (int16_t)ply;
             if (p.game_counts) {
-                p.game_counts[2 * game] = (uint8_t)popc(e.black);
-                p.game_counts[2 * game + 1] = (uint8_t)popc(e.white);
+                p.game_counts[2 * game] = (int16_t)popc(e.black);
+                p.game_counts[2 * game + 1] = (int16_t)popc(e.white);
             }
         }
     }

@@ -50,7 +50,7 @@ def rollout(num_envs, black, white, board_size=8, initial_rand_steps=10, games_p
     if record:
         rec = {"result": torch.zeros((games,), dtype=torch.int8, device=dev),
                "plies": torch.zeros((games,), dtype=torch.int16, device=dev),
-               "counts": torch.zeros((games, 2), dtype=torch.uint8, device=dev)}
+               "counts": torch.zeros((games, 2), dtype=torch.int16, device=dev)}
         ptrs[:3] = [_cabi.ptr(rec["result"]), _cabi.ptr(rec["plies"]), _cabi.ptr(rec["counts"])]
         if trace_len:
             stride = int(trace_len)

@@ -41,7 +41,7 @@ extern "C" {
 
 #define OTH_ABI_VERSION 1
 #define OTH_MIN_BOARD_SIZE 4   /* othello.py:230 clamps to >= 4 */
-#define OTH_MAX_BOARD_SIZE 12
+#define OTH_MAX_BOARD_SIZE 16   /* 256 cells = 4 words per colour; actions fit the int16 traces */
 
 typedef struct oth_state {
     uint64_t *black;   /* [W][B] */
@@ -158,11 +158,11 @@ int oth_policy(oth_state st, int64_t B, int board_size, oth_policy_spec spec, ui
  * policy vs white policy, first max_rand_steps plies uniformly random; no state is read
  * or written, only tally[0..3] += {black wins, draws, white wins, plies} (atomics; the
  * buffer is the NCCL all-reduce send buffer).  Optional per-game records for tests:
- * game_result[g] (int8 winner), game_plies[g] (int16), game_counts[2g..] (uint8 black, white discs),
+ * game_result[g] (int8 winner), game_plies[g] (int16), game_counts[2g..] (int16 black, white discs; 16x16 holds up to 256),
  * trace[g*trace_stride + ply] (int16 action applied), with g = i*games_per_env + k. */
 int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec black, oth_policy_spec white,
                 int init_rand_steps, int games_per_env, uint64_t seed, int64_t env_id_base,
-                unsigned long long *tally, int8_t *game_result, int16_t *game_plies, uint8_t *game_counts,
+                unsigned long long *tally, int8_t *game_result, int16_t *game_plies, int16_t *game_counts,
                 int16_t *trace, int trace_stride, void *stream);
 
 /* set_board_state + set_player_turn (othello.py:380-389,464-466): dense cells [B][S*S]

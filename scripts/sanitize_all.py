@@ -39,7 +39,7 @@ def main():
     dev = "cuda:0"
     t0 = time.time()
     launches = 0
-    sizes = (5, 6, 8, 9, 12) if a.quick else tuple(range(4, 13))
+    sizes = (5, 6, 8, 9, 12, 16) if a.quick else tuple(range(4, 17))
     steps = 3 if a.quick else 6
     layouts = ("none", "board", "board+mask", "planes4", "planes3", "absolute")
     for S in sizes:

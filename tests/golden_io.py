@@ -10,8 +10,8 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 _EP_KEYS = ("cfg", "act", "rew", "done", "board", "turn", "legal", "obs", "winner", "cnt", "state4")
 
 
-def load_trajectories():
-    z = np.load(os.path.join(GOLDEN, "trajectories.npz"))
+def _load_episodes(fname):
+    z = np.load(os.path.join(GOLDEN, fname))
     eps = []
     for i in range(int(z["num_episodes"])):
         e = {}
@@ -25,12 +25,18 @@ def load_trajectories():
     return eps
 
 
+def load_trajectories():
+    """Board sizes 4..12 (make_golden.py) followed by 13..16 (make_golden_large.py)."""
+    return _load_episodes("trajectories.npz") + _load_episodes("trajectories_large.npz")
+
+
 def load_policies():
-    z = np.load(os.path.join(GOLDEN, "policies.npz"))
     out = {}
-    for S in z["sizes"]:
-        S = int(S)
-        out[S] = dict(board=z["s%d_board" % S], turn=z["s%d_turn" % S], choice=z["s%d_choice" % S])
+    for fname in ("policies.npz", "policies_large.npz"):
+        z = np.load(os.path.join(GOLDEN, fname))
+        for S in z["sizes"]:
+            S = int(S)
+            out[S] = dict(board=z["s%d_board" % S], turn=z["s%d_turn" % S], choice=z["s%d_choice" % S])
     return out
 
 

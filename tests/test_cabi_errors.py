@@ -68,12 +68,12 @@ def test_header_error_codes_match():
     assert int(codes["OTH_ERR_CUDA"]) == 2000
 
 
-@pytest.mark.parametrize("S", [-1, 0, 3, 13, 64])
+@pytest.mark.parametrize("S", [-1, 0, 3, 17, 64])
 def test_unsupported_board_size_everywhere(lib, S):
     """The C ABI does not clamp (the Python classes do, othello.py:230): sizes outside the build are an error."""
     assert lib.oth_words_per_board(S) == 0
     assert lib.oth_reset(_state(), 8, S, 0, 0, 0, 1, None, None) == ERR_BAD_BOARD_SIZE
-    assert "board_size %d unsupported" % S in _err(lib) and "4..12" in _err(lib)
+    assert "board_size %d unsupported" % S in _err(lib) and "4..16" in _err(lib)
     assert lib.oth_observe(_state(), 8, S, 0, _outputs(), None) == ERR_BAD_BOARD_SIZE
     assert lib.oth_step(_state(), 8, S, 0, _cabi.ACT_RANDOM, None, 0, 0, 0, _outputs(), None) == ERR_BAD_BOARD_SIZE
     assert lib.oth_policy(_state(), 8, S, _spec(), 0, 0, 0, FAKE, None) == ERR_BAD_BOARD_SIZE
@@ -215,7 +215,7 @@ def test_last_error_is_thread_local(lib):
 
 
 def test_python_host_raises_with_the_library_message(lib):
-    rc = lib.oth_reset(_state(), 8, 13, 0, 0, 0, 1, None, None)
-    with pytest.raises(_cabi.OthelloB200Error, match=r"oth_reset failed \(code 1002\): board_size 13 unsupported"):
+    rc = lib.oth_reset(_state(), 8, 17, 0, 0, 0, 1, None, None)
+    with pytest.raises(_cabi.OthelloB200Error, match=r"oth_reset failed \(code 1002\): board_size 17 unsupported"):
         _cabi.check(rc, "oth_reset")
     _cabi.check(0, "oth_reset")

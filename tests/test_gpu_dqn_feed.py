@@ -29,7 +29,7 @@ def _reference_exploit(q, legal):
     return out
 
 
-@pytest.mark.parametrize("S", [8, 6, 10, 12, 5])
+@pytest.mark.parametrize("S", [8, 6, 10, 12, 5, 13, 16])
 def test_epsilon_greedy_exploit_explore_and_philox_prediction(S):
     from gymothelloenv_b200 import epsilon_greedy
     B, seed, base, counter = 6000, 77, 1 << 33, 5

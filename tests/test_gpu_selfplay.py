@@ -53,7 +53,8 @@ def test_ppoenvs_reproduces_live_reference(c):
     envs.over()
 
 
-@pytest.mark.parametrize("S,disk,legacy", [(8, True, True), (8, False, False), (6, True, True), (5, True, False), (10, True, True)])
+@pytest.mark.parametrize("S,disk,legacy", [(8, True, True), (8, False, False), (6, True, True), (5, True, False), (10, True, True),
+                                           (13, True, True), (16, False, True)])
 def test_ppoenvs_vs_oracle_mixed_protagonists(S, disk, legacy):
     B = 384
     rng = np.random.RandomState(S * 7 + disk)
@@ -163,7 +164,7 @@ def _torch_logp(logits, legal):
     return torch.log_softmax(x.masked_fill(~m, float("-inf")), dim=1).numpy()
 
 
-@pytest.mark.parametrize("S", [8, 6, 10, 12, 5])
+@pytest.mark.parametrize("S", [8, 6, 10, 12, 5, 14, 16])
 def test_masked_categorical_modes(S):
     from gymothelloenv_b200 import masked_categorical
     B, seed = 5000, 1234

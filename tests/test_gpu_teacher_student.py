@@ -46,7 +46,7 @@ def test_device_reproduces_live_reference(c):
 
 
 @pytest.mark.parametrize("S,disk,legacy", [(8, True, True), (8, False, False), (6, True, True), (10, False, True),
-                                           (5, True, False), (12, True, True)])
+                                           (5, True, False), (12, True, True), (15, True, True)])
 def test_device_vs_oracle_large_batch(S, disk, legacy):
     B = 320
     envs = _mk(B, S, disk, legacy)

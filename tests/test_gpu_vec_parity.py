@@ -125,7 +125,8 @@ def _compare(env, orc, live_before, ctx):
 
 
 FUZZ = [(8, 1, 0, 0.0), (8, 1, 1, 0.02), (8, 0, 0, 0.2), (4, 1, 0, 0.02), (5, 0, 1, 0.1), (6, 1, 1, 0.02),
-        (7, 1, 0, 0.02), (9, 0, 0, 0.1), (10, 1, 1, 0.01), (11, 1, 0, 0.02), (12, 1, 1, 0.01), (12, 0, 0, 0.1)]
+        (7, 1, 0, 0.02), (9, 0, 0, 0.1), (10, 1, 1, 0.01), (11, 1, 0, 0.02), (12, 1, 1, 0.01), (12, 0, 0, 0.1),
+        (13, 1, 1, 0.01), (14, 0, 0, 0.1), (15, 1, 0, 0.02), (16, 1, 1, 0.01), (16, 0, 0, 0.1)]
 
 
 @pytest.mark.parametrize("S,sudden,disk,p_invalid", FUZZ)
@@ -157,7 +158,7 @@ def test_random_streams_vs_oracle(S, sudden, disk, p_invalid):
     assert steps > B * (N - 10) * (0.5 if p_invalid else 0.9) or sudden
 
 
-@pytest.mark.parametrize("S", [6, 8, 10, 5, 7, 9, 11, 12, 4])
+@pytest.mark.parametrize("S", [6, 8, 10, 5, 7, 9, 11, 12, 4, 13, 14, 15, 16])
 def test_auto_reset_and_all_layouts(S):
     """auto_reset: the terminal transition reports reward/done/winner, the state restarts
     in the same call; every obs layout x dtype equals the oracle's observation."""
@@ -197,7 +198,8 @@ def test_auto_reset_and_all_layouts(S):
 
 # --------------------------------------------------------------------------- policies
 @pytest.mark.parametrize("S,depths", [(8, (1, 2, 3)), (6, (1, 2, 3, 4)), (4, (1, 2, 3, 4)), (5, (2, 3)), (10, (1, 2)),
-                                      (12, (1, 2)), (9, (2,)), (7, (3,)), (11, (2,))])
+                                      (12, (1, 2)), (9, (2,)), (7, (3,)), (11, (2,)), (13, (1, 2)), (14, (2,)), (15, (1,)),
+                                      (16, (1, 2))])
 def test_policy_choices_vs_oracle(S, depths):
     """greedy / maximin-k pick the same action index as the oracle on positions reached by
     random play (incl. forced passes and near-terminal boards)."""

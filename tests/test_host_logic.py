@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol():
     lib.oth_abi_version.restype = ctypes.c_int
     lib.oth_words_per_board.restype = ctypes.c_int
     assert lib.oth_abi_version() == 1                       # no GPU needed for these two
-    assert [lib.oth_words_per_board(s) for s in (3, 4, 8, 9, 11, 12, 13)] == [0, 1, 1, 2, 2, 3, 0]
+    assert [lib.oth_words_per_board(s) for s in (3, 4, 8, 9, 11, 12, 13, 14, 16, 17)] == [0, 1, 1, 2, 2, 3, 3, 4, 4, 0]
 
 
 def test_header_constants_match_python_binding():
