@@ -74,7 +74,7 @@ ROLLOUT_CASES = [
     (6, "maximin4", "rand", 0, 64), (10, "greedy", "rand", 10, 160), (12, "rand", "maximin2", 8, 48),
     (5, "maximin2", "greedy", 4, 200), (4, "maximin4", "maximin3", 2, 100), (9, "greedy", "greedy", 10, 64),
     (8, "maximin2", "maximin3", 10, 96), (8, "rand", "maximin4", 10, 33), (7, "maximin3", "maximin3", 2, 130),
-    (13, "greedy", "rand", 10, 64), (14, "rand", "greedy", 6, 64), (16, "greedy", "maximin2", 10, 24), (15, "rand", "rand", 0, 96),
+    (13, "greedy", "rand", 10, 64), (14, "rand", "greedy", 6, 64), (16, "greedy", "maximin2", 10, 8), (15, "rand", "rand", 0, 96),
 ]
 
 

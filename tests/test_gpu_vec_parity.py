@@ -199,11 +199,11 @@ def test_auto_reset_and_all_layouts(S):
 # --------------------------------------------------------------------------- policies
 @pytest.mark.parametrize("S,depths", [(8, (1, 2, 3)), (6, (1, 2, 3, 4)), (4, (1, 2, 3, 4)), (5, (2, 3)), (10, (1, 2)),
                                       (12, (1, 2)), (9, (2,)), (7, (3,)), (11, (2,)), (13, (1, 2)), (14, (2,)), (15, (1,)),
-                                      (16, (1, 2))])
+                                      (16, (1,))])
 def test_policy_choices_vs_oracle(S, depths):
     """greedy / maximin-k pick the same action index as the oracle on positions reached by
     random play (incl. forced passes and near-terminal boards)."""
-    B, N = 384, S * S
+    B, N = (384 if S <= 12 else 96), S * S     # the oracle's cell-walk maximin is the slow side on large boards
     rng = np.random.default_rng(99 + S)
     env = _env(num_envs=B, board_size=S)
     orc = oracle.OracleVec(B, S)
