@@ -293,11 +293,11 @@ def run_ours(args):
     twin = VecOthelloEnv(B, board_size=8, device=dev, seed=0, auto_reset=True, obs_layout="board",
                          obs_dtype=torch.int8, env_id_base=rank * B)
     twin.set_state(env.get_state())
-    host_actions = torch.empty((Ke + 3, B), dtype=torch.int64, pin_memory=True)
+    host_actions = torch.empty((Ke + 3, B), dtype=torch.int16, pin_memory=True)   # an action is 0..63: 2 bytes on PCIe
     saved = env.get_state()
     for s in range(Ke + 3):                        # the action stream the device policy would play
         env.step(policy="random")
-        host_actions[s].copy_(env.actions_taken, non_blocking=True)
+        host_actions[s].copy_(env.actions_taken.to(torch.int16), non_blocking=True)
     torch.cuda.synchronize(dev)
     twin.set_state(saved)
     for s in range(3):

@@ -220,7 +220,9 @@ class VecOthelloEnv(object):
     # ------------------------------------------------------------------ host-buffer path
     def step_host(self, actions_host):
         """The same step through HOST buffers: pinned H2D of the actions, kernel, pinned D2H
-        of obs / legal mask / reward / done.  `actions_host`: pinned int64 CPU tensor [B].
+        of obs / legal mask / reward / done.  `actions_host`: pinned integer CPU tensor [B]; int64 like the
+        device API, or a narrower signed type (int16 holds every action of a 16x16 board and -1): it then
+        crosses PCIe at its own width and is widened on the device.
         Returns CPU tensors (pinned, reused across calls)."""
         if self._host is None:
             pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True)   # noqa: E731
@@ -231,7 +233,17 @@ class VecOthelloEnv(object):
                 "reward": pin(self.reward), "done": pin(self._done_u8),
             }
         h = self._host
-        h["actions_dev"].copy_(actions_host, non_blocking=True)
+        if actions_host.dtype == torch.int64:
+            h["actions_dev"].copy_(actions_host, non_blocking=True)
+        else:
+            if actions_host.dtype not in (torch.int8, torch.int16, torch.int32):
+                raise TypeError("actions_host must be a signed integer tensor")
+            key = "actions_" + str(actions_host.dtype)
+            if key not in h:
+                h[key] = torch.empty((self.num_envs,), dtype=actions_host.dtype, device=self.device)
+            h[key].copy_(actions_host, non_blocking=True)       # H2D at the narrow width
+            h["actions_dev"].copy_(h[key])                       # widened on the device
+        self._host_action_bytes = actions_host.element_size()
         self.step(h["actions_dev"])
         if h["obs"] is not None:
             h["obs"].copy_(self.obs, non_blocking=True)
@@ -243,13 +255,13 @@ class VecOthelloEnv(object):
         return h["obs"], h["reward"], h["done"], h["mask"]
 
     def host_bytes_per_step(self):
-        """(h2d, d2h) bytes moved by one step_host() call."""
+        """(h2d, d2h) bytes moved by one step_host() call (h2d at the width of the last actions_host passed)."""
         d2h = self.reward.numel() * 4 + self._done_u8.numel()
         if self.obs is not None:
             d2h += self.obs.numel() * self.obs.element_size()
         if self._mask_u8 is not None:
             d2h += self._mask_u8.numel()
-        return self.num_envs * 8, d2h
+        return self.num_envs * getattr(self, "_host_action_bytes", 8), d2h
 
     # ------------------------------------------------------------------ accessors
     def observe(self, layout=None, dtype=None, out=None):

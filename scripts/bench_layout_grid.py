@@ -7,7 +7,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gymothelloenv_b200 import VecOthelloEnv
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 18
 PLANES = {"board": 1, "board+mask": 2, "planes4": 4, "planes3": 3}
-for S in range(4, 13):
+for S in range(4, 17):
     row = {"S": S}
     for layout, P in PLANES.items():
         for dname, dt, es in (("i8", torch.int8, 1), ("f32", torch.float32, 4)):

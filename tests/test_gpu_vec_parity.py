@@ -339,6 +339,17 @@ def test_host_buffer_step_matches_device_step():
     assert torch.equal(rew_h, e1.reward.cpu()) and torch.equal(done_h, e1._done_u8.cpu())
     h2d, d2h = e2.host_bytes_per_step()
     assert h2d == 8 * B and d2h == B * (64 + 64 + 4 + 1)
+    # narrow host actions (int16 / int8 / int32) cross PCIe at their own width and play the same ply
+    for dt, width in ((torch.int16, 2), (torch.int8, 1), (torch.int32, 4)):
+        acts = e1.policy_actions("greedy")
+        acts[::9] = -1                                         # an invalid action survives the narrowing
+        e1.step(acts)
+        obs_h, rew_h, done_h, mask_h = e2.step_host(acts.to(dt).cpu().pin_memory())
+        assert torch.equal(obs_h, e1.obs.cpu()) and torch.equal(mask_h, e1._mask_u8.cpu())
+        assert torch.equal(rew_h, e1.reward.cpu()) and torch.equal(done_h, e1._done_u8.cpu())
+        assert e2.host_bytes_per_step()[0] == width * B
+    with pytest.raises(TypeError):
+        e2.step_host(torch.zeros(B, dtype=torch.uint8).pin_memory())
 
 
 def test_perft_through_the_engine():
