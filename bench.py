@@ -287,6 +287,22 @@ def run_ours(args):
     alu_peak = n_instr.value / (a.elapsed_time(b) * 1e-3)
     alu = {"int32_alu_peak_measured_inst_per_s": alu_peak, "sms": sms,
            "note": "LOP3/SHF/IADD stream, 8x256 threads per SM; see profiles/ for the instruction count per env step"}
+    # the other roofline north_star names: ALU-pipe instructions k_step<8> executes per launch (an ncu count committed
+    # under profiles/, NOT measured in this run) over this run's measured step time, against the pipe's issue limit
+    # (16 lanes per SM sub-partition per clock = one warp instruction every 2 clocks) at the clock sampled under load
+    alu_path = os.path.join(ROOT, "profiles", "alu_pipe.json")
+    if os.path.isfile(alu_path):
+        try:
+            aj = json.load(open(alu_path))
+            scale = B / float(aj["envs_per_launch"])
+            inst = aj["k_step_8_alu_pipe_warp_inst_per_launch"] * scale
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            pipe_peak = sms * 4 * 0.5 * mhz * 1e6                      # warp instructions / s
+            alu.update({"alu_pipe_warp_inst_per_launch": inst, "alu_pipe_peak_warp_inst_per_s": pipe_peak,
+                        "alu_pipe_frac": inst / (kernel_ms * 1e-3) / pipe_peak,
+                        "alu_pipe_active_pct_ncu": aj["k_step_8_alu_pipe_active_pct"], "count_source": aj["source"]})
+        except Exception:
+            pass
 
     # ---- e2e through host buffers ----
     Ke = max(3, args.e2e_steps)

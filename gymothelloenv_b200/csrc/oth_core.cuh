@@ -13,7 +13,7 @@
 //   maximin_pick simple_policies.py:111-163
 // The algorithm is NOT the reference's cell-by-cell ray walk: east/west moves and all flips come
 // from carry propagation (an add ripples through a run of opponent discs), the other move axes
-// from paired Kogge-Stone occluded fills (shift + mask); popcounts give the scores.
+// from Kogge-Stone occluded fills (shift + mask); popcounts give the scores.
 #pragma once
 #include <stdint.h>
 #include "../../include/othello_b200.h"
@@ -150,31 +150,36 @@ OTH_DEV BB<W> sh(const BB<W> &a) {
 // the carry ripple through each bracket-able run and land on the cell behind it (edge
 // columns are 0 in the mask and a row is S contiguous bits, so a carry never leaves its
 // row).  West = the same on bit-reversed boards (BREV runs off the ALU pipe; the reversed
-// board sits in the top S*S bits, rows still contiguous).  The three other axes use paired
-// Kogge-Stone fills (steps 1, 2, 2 cover the longest run, S-2 <= 6) that share the doubled
-// propagator between the two opposite directions.
+// board sits in the top S*S bits, rows still contiguous).  The three other axes use Kogge-Stone
+// occluded fills (steps 1, 2, 2 cover the longest run, S-2 <= 6), upward on the normal boards and
+// -- for the three downward directions -- upward on the reversed boards.
+// One direction only, towards higher bit indices: a Kogge-Stone occluded fill, reach 2, 4, 6 cells.
+// A 64-bit LEFT shift is one IMAD.SHL (low half, FMA pipe) + one SHF (high half, ALU pipe); a RIGHT shift is two
+// SHF on the ALU pipe, the binding unit of k_step.  legal1 therefore runs the downward directions as upward fills
+// on the bit-reversed boards (BREV is on the XU pipe) and reverses the union once.
 template <int D>
-OTH_DEV u64 pair_moves1(u64 P, u64 m) {
-    u64 fl = m & (P << D), fr = m & (P >> D);
-    fl |= m & (fl << D);
-    fr |= m & (fr >> D);
-    const u64 pl = m & (m << D), pr = pl >> D;
-    fl |= pl & (fl << (2 * D));
-    fr |= pr & (fr >> (2 * D));
-    fl |= pl & (fl << (2 * D));
-    fr |= pr & (fr >> (2 * D));
-    return (fl << D) | (fr >> D);
+OTH_DEV u64 fill_up1(u64 P, u64 m) {
+    u64 f = m & (P << D);
+    f |= m & (f << D);
+    const u64 pl = m & (m << D);
+    f |= pl & (f << (2 * D));
+    f |= pl & (f << (2 * D));
+    return f << D;
 }
 template <int S>
 OTH_DEV u64 legal1(u64 P, u64 O) {
     static_assert(Geo<S>::W == 1, "single-word boards only");
     const u64 Oi = O & GeoWord<S, 0>::inner;
-    u64 moves = (Oi + ((P << 1) & Oi)) & ~Oi;
-    const u64 Pr = __brevll(P), Or = __brevll(Oi);
-    moves |= __brevll((Or + ((Pr << 1) & Or)) & ~Or);
-    moves |= pair_moves1<S>(P, O);
-    moves |= pair_moves1<S - 1>(P, Oi);
-    moves |= pair_moves1<S + 1>(P, Oi);
+    const u64 Pr = __brevll(P), Or = __brevll(O), Oir = __brevll(Oi);
+    u64 up = (Oi + ((P << 1) & Oi)) & ~Oi;                 // east: carry through the opponent run
+    up |= fill_up1<S>(P, O);
+    up |= fill_up1<S - 1>(P, Oi);
+    up |= fill_up1<S + 1>(P, Oi);
+    u64 dn = (Oir + ((Pr << 1) & Oir)) & ~Oir;             // west = east on the reversed board, and so on
+    dn |= fill_up1<S>(Pr, Or);
+    dn |= fill_up1<S - 1>(Pr, Oir);
+    dn |= fill_up1<S + 1>(Pr, Oir);
+    const u64 moves = up | __brevll(dn);
     if constexpr (S == 8) return moves & ~(P | O);
     else return moves & ~(P | O) & GeoWord<S, 0>::full;
 }
