@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=30)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true",
+                    help="replay a one-step CUDA graph per timed step instead of a Python -> ctypes launch "
+                         "(measured identical: 45.05 vs 45.06 us, the loop is not host-paced)")
     ap.add_argument("--profile-timed-region", action="store_true",
                     help="cudaProfilerStart/Stop around the K timed steps (ncu --profile-from-start off then lists "
                          "exactly the launches of the timed region)")
@@ -214,6 +217,12 @@ def run_ours(args):
     # ---- warm-up, then EXACTLY K timed steps (one launch each) ----
     for _ in range(W):
         env.step(policy="random")
+    # --graph: the timed loop replays a ONE-step CUDA graph (same kernel, same arguments) -- a check that the
+    # Python -> ctypes launch path does not pace the back-to-back launches (it does not: profiles/r02i_graph.md)
+    step_graph = env.capture_steps("random", 1) if args.graph else None
+    if step_graph is not None:
+        for _ in range(3):
+            step_graph.replay()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -226,8 +235,12 @@ def run_ours(args):
     if args.profile_timed_region:
         torch.cuda.profiler.start()
     ev0.record()
-    for _ in range(K):
-        env.step(policy="random")
+    if step_graph is None:
+        for _ in range(K):
+            env.step(policy="random")
+    else:
+        for _ in range(K):
+            step_graph.replay()                  # one k_step<8> launch per replay
     ev1.record()
     barrier()
     if args.profile_timed_region:
@@ -357,7 +370,9 @@ def run_ours(args):
                        "auto_reset": True, "obs": "int8 (B,8,8) + bool mask (B,64)",
                        "l2": "working set per step %.0f MB > 126 MB L2 (state 32 B + outputs 143 B per env)"
                              % (B * (32 + 143) / 1e6),
-                       "finished_games_per_step_frac": frac_done},
+                       "finished_games_per_step_frac": frac_done,
+                       "launch": ("python -> ctypes launch per step" if step_graph is None
+                                  else "one-step CUDA graph replayed per step (VecOthelloEnv.capture_steps)")},
             "roofline": roofline, "alu": alu, "cpu_baseline": cpu, "cpu_baseline_c": cpu_c, "e2e": e2e,
             "gpu_launches": K, "clocks": clocks, "total_env_steps": int(counters[0].item()),
         }
