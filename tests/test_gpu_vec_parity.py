@@ -381,3 +381,22 @@ def test_perft_through_the_engine():
                 keep_t = turns[(legal.sum(1) == 0) | term]
                 nb = np.concatenate([nb, keep_b]); nt = np.concatenate([nt, keep_t])
             boards, turns = nb, nt
+
+
+def test_captured_step_graph_replays_the_same_plies():
+    """VecOthelloEnv.capture_steps: replaying a CUDA graph of k fused policy+step launches plays exactly the plies
+    k eager calls play (the Philox position lives in the env state, not in launch arguments)."""
+    kw = dict(num_envs=3000, board_size=8, seed=9, auto_reset=True, initial_rand_steps=4)
+    eager, graphed = _env(**kw), _env(**kw)
+    eager.reset(); graphed.reset()
+    g = graphed.capture_steps("random", steps=4)
+    for _ in range(20):
+        eager.step(policy="random")
+    for _ in range(5):
+        g.replay()
+    torch.cuda.synchronize()
+    for name in ("_black", "_white", "_legal", "_meta", "_ctr"):
+        assert torch.equal(getattr(eager, name), getattr(graphed, name)), name
+    assert torch.equal(eager.obs, graphed.obs) and torch.equal(eager._mask_u8, graphed._mask_u8)
+    with pytest.raises(ValueError):
+        graphed.capture_steps("maximin")
