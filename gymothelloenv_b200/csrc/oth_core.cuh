@@ -188,6 +188,18 @@ OTH_DEV u64 legal1(u64 P, u64 O) {
 // The single-word tricks carry over once add / subtract / bit-reverse work on the whole W-word
 // board: a row is still S contiguous bits (it may straddle a word boundary, which is why the
 // carry must run through all words), and the bit-reversed board still has contiguous rows.
+#ifdef OTH_HOST_EMUL   // tests/host_emul: the same carry chains in portable C++ (never part of the product build)
+template <int W> OTH_DEV BB<W> bb_add(const BB<W> &a, const BB<W> &b) {
+    BB<W> r; unsigned c = 0;
+    BB_FOR(i) { const unsigned __int128 t = (unsigned __int128)a.w[i] + b.w[i] + c; r.w[i] = (u64)t; c = (unsigned)(t >> 64); }
+    return r;
+}
+template <int W> OTH_DEV BB<W> bb_sub(const BB<W> &a, const BB<W> &b) {
+    BB<W> r; unsigned c = 0;
+    BB_FOR(i) { const unsigned __int128 t = (unsigned __int128)a.w[i] - b.w[i] - c; r.w[i] = (u64)t; c = (unsigned)(t >> 64) & 1u; }
+    return r;
+}
+#else
 template <int W> OTH_DEV BB<W> bb_add(const BB<W> &a, const BB<W> &b) {
     BB<W> r;
     if constexpr (W == 1) {
@@ -226,6 +238,7 @@ template <int W> OTH_DEV BB<W> bb_sub(const BB<W> &a, const BB<W> &b) {
     }
     return r;
 }
+#endif
 template <int W> OTH_DEV BB<W> bb_one(u64 v) { BB<W> r; BB_FOR(i) r.w[i] = i == 0 ? v : 0ull; return r; }
 // bit j -> bit 64*W - 1 - j
 template <int W> OTH_DEV BB<W> bb_brev(const BB<W> &a) { BB<W> r; BB_FOR(i) r.w[i] = __brevll(a.w[W - 1 - i]); return r; }
