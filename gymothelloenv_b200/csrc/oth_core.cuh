@@ -318,6 +318,40 @@ struct GeoRays {
     static constexpr u64 e = geo_ray_pattern(S, 1), s = geo_ray_pattern(S, S);
     static constexpr u64 se = geo_ray_pattern(S, S + 1), sw = geo_ray_pattern(S, S - 1);
 };
+#ifndef OTH_FLIPS_STOP_MUL
+#define OTH_FLIPS_STOP_MUL 1    // 0: the round-1 form (compare + select per ray), kept for A/B timing
+#endif
+#if OTH_FLIPS_STOP_MUL
+// the closing own disc of one ray (0 if the run is not bracketed): see above
+OTH_DEV u64 ray_stop1(u64 m, u64 P, u64 O) {
+    const u64 x = O | ~m;
+    const u64 t = x + 1ull;
+    return t & ~x & P;
+}
+// The discs a ray turns, rebuilt from its closing disc WITHOUT a compare / select: on the bit-reversed board the
+// closing disc lies BELOW the move and the turned discs are the ray cells from it up to the move, i.e.
+// (brev(stop) * pattern) & (brev(mv) - 1) -- the product is 0 when the ray is open, the 64-bit multiply runs on the
+// FMA pipe and the reversal on the XU pipe, so a ray costs 6 ALU-pipe instructions (O|~m, +1, &) plus its share of
+// one OR / AND per half instead of 14.  The four rays of one orientation share the AND with the cells below the
+// move; their result comes out in the OTHER orientation.
+template <int S>
+OTH_DEV u64 flips1_half(u64 mv, u64 mv_other, u64 P, u64 O, u64 Oi) {
+    u64 f = __brevll(ray_stop1(mv * GeoRays<S>::e, P, Oi)) * GeoRays<S>::e;
+    f |= __brevll(ray_stop1(mv * GeoRays<S>::s, P, O)) * GeoRays<S>::s;
+    f |= __brevll(ray_stop1(mv * GeoRays<S>::se, P, Oi)) * GeoRays<S>::se;
+    f |= __brevll(ray_stop1(mv * GeoRays<S>::sw, P, Oi)) * GeoRays<S>::sw;
+    return f & (mv_other - 1ull);          // mv_other = brev(mv); mv == 0 gives stops 0, hence f == 0
+}
+template <int S>
+OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
+    static_assert(Geo<S>::W == 1, "single-word boards only");
+    const u64 Oi = O & GeoWord<S, 0>::inner;
+    const u64 mvr = __brevll(mv);
+    const u64 dn_rev = flips1_half<S>(mv, mvr, P, O, Oi);                                 // rays towards higher indices
+    const u64 up = flips1_half<S>(mvr, mv, __brevll(P), __brevll(O), __brevll(Oi));      // rays towards lower indices
+    return up | __brevll(dn_rev);
+}
+#else
 OTH_DEV u64 ray_flips1(u64 m, u64 P, u64 O) {
     const u64 x = O | ~m;
     const u64 t = x + 1ull;
@@ -340,6 +374,8 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
     const u64 dn = flips1_up<S>(__brevll(mv), __brevll(P), __brevll(O), __brevll(Oi));
     return up | __brevll(dn);
 }
+
+#endif
 
 // ---- multi-word boards: flips by carry propagation -------------------------------------
 // whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
