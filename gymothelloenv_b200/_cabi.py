@@ -8,8 +8,11 @@ import ctypes as C
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "_lib", "libothello_b200.so")
+# OTH_LIB_DIR (development only): directory name of an A/B variant build made by scripts/build_variant.py
+_VARIANT = os.environ.get("OTH_LIB_DIR")
+LIB_PATH = os.path.join(_PKG, _VARIANT or "_lib", "libothello_b200.so")
 
+ABI_VERSION = 2
 MIN_BOARD_SIZE = 4
 MAX_BOARD_SIZE = 16
 
@@ -60,7 +63,7 @@ class OthState(C.Structure):
 class OthOutputs(C.Structure):
     _fields_ = [("obs", C.c_void_p), ("legal_mask", C.c_void_p), ("reward", C.c_void_p), ("done", C.c_void_p),
                 ("player_turn", C.c_void_p), ("winner", C.c_void_p), ("actions_out", C.c_void_p),
-                ("obs_layout", C.c_int32), ("obs_dtype", C.c_int32)]
+                ("obs_layout", C.c_int32), ("obs_dtype", C.c_int32), ("packed", C.c_void_p)]
 
 
 class OthSelfPlay(C.Structure):
@@ -96,6 +99,16 @@ def load():
         raise OthelloB200Error(
             "libothello_b200.so is missing (%s). Build it with `python -m gymothelloenv_b200.build` "
             "(needs nvcc; targets sm_100a). There is no CPU fallback." % LIB_PATH)
+    if not _VARIANT:
+        # a library built from other sources than the ones on disk has produced wrong conclusions before: refuse it
+        from . import build as _build
+        stamp = LIB_PATH + ".digest"
+        have = open(stamp).read().strip() if os.path.isfile(stamp) else None
+        want = _build.source_digest()
+        if have != want:
+            raise OthelloB200Error(
+                "libothello_b200.so is stale: built from sources with digest %s, the tree has %s. Rebuild with "
+                "`python -m gymothelloenv_b200.build`." % (have and have[:12], want[:12]))
     L = C.CDLL(LIB_PATH)
     L.oth_abi_version.restype = C.c_int
     L.oth_last_error.restype = C.c_char_p
@@ -149,7 +162,7 @@ def load():
     L.oth_ts_advance.argtypes = [OthState, OthTeacherStudent, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int64, C.c_int,
                                  OthOutputs, C.c_void_p, C.c_void_p]
-    if L.oth_abi_version() != 1:
+    if L.oth_abi_version() != ABI_VERSION:
         raise OthelloB200Error("libothello_b200.so ABI version mismatch")
     _lib = L
     return L

@@ -65,17 +65,30 @@ def _compile(args):
     return obj
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, only_sizes=None, reuse_obj_dir=None):
+    """only_sizes / reuse_obj_dir: A/B variant builds (scripts/build_variant.py) recompile a few sizes and link the
+    other sizes' objects from an existing build."""
     if not force and is_fresh():
         return LIB_PATH
     os.makedirs(OBJ_DIR, exist_ok=True)
     jobs = [(os.path.join(CSRC, "oth_size.cu"), os.path.join(OBJ_DIR, "oth_size_%d.o" % s), ["-DOTH_S=%d" % s])
             for s in BOARD_SIZES]
     jobs.append((os.path.join(CSRC, "oth_cabi.cu"), os.path.join(OBJ_DIR, "oth_cabi.o"), []))
+    reused = []
+    if only_sizes is not None:
+        keep = []
+        for j in jobs:
+            size = int(j[2][0].split("=")[1]) if j[2] else None
+            if size is None or size in only_sizes:
+                keep.append(j)
+            else:
+                shutil.copyfile(os.path.join(reuse_obj_dir, os.path.basename(j[1])), j[1])
+                reused.append(j[1])
+        jobs = keep
     # big boards first: they take the longest
     jobs.sort(key=lambda j: -int(j[2][0].split("=")[1]) if j[2] else 0)
     with cf.ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 4))) as ex:
-        objs = list(ex.map(_compile, jobs))
+        objs = list(ex.map(_compile, jobs)) + reused
     tmp = LIB_PATH + ".tmp%d" % os.getpid()
     cmd = [_nvcc(), "-shared", "-o", tmp] + sorted(objs) + ["-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

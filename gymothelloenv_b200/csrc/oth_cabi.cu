@@ -62,6 +62,8 @@ static int check_outputs(const oth_outputs &o) {
     }
     if (o.legal_mask != nullptr && ((uintptr_t)o.legal_mask & 15u) != 0)
         return fail(OTH_ERR_BAD_ARG, "legal_mask must be 16-byte aligned");
+    if (o.packed != nullptr && ((uintptr_t)o.packed & 15u) != 0)
+        return fail(OTH_ERR_BAD_ARG, "packed must be 16-byte aligned");
     return 0;
 }
 

@@ -717,6 +717,37 @@ OTH_DEV EnvRegs<S> empty_env() {
     return e;
 }
 
+// ------------------------------------------------------------------- per-env scalars
+// out.packed: one 16-byte record per env (include/othello_b200.h) = ONE address and one STG.128 instead of five
+// stores with five 64-bit address computations; the separate arrays are still served when they are not null.
+OTH_DEV u32 pack_status(int done, int turn, int winner) {
+    return (u32)(done & 0xFF) | ((u32)(turn & 0xFF) << 8) | ((u32)(winner & 0xFF) << 16);
+}
+template <bool PACKED_ONLY>
+OTH_DEV void put_step_scalars(const oth_outputs &o, i64 i, int reward, int done, int turn, int winner, i64 action) {
+    if (PACKED_ONLY || o.packed != nullptr)
+        reinterpret_cast<uint4 *>(o.packed)[i] = make_uint4(__float_as_uint((float)reward), pack_status(done, turn, winner),
+                                                            (u32)(u64)action, (u32)((u64)action >> 32));
+    if constexpr (!PACKED_ONLY) {
+        if (o.reward) o.reward[i] = (float)reward;
+        if (o.done) o.done[i] = (uint8_t)done;
+        if (o.player_turn) o.player_turn[i] = (int8_t)turn;
+        if (o.winner) o.winner[i] = (int8_t)winner;
+        if (o.actions_out) o.actions_out[i] = action;
+    }
+}
+// calls that produce no reward / action (oth_observe, the protocol kernels): status bytes only
+OTH_DEV void put_status(const oth_outputs &o, i64 i, int done, int turn, int winner, bool with_winner) {
+    if (o.packed != nullptr) {
+        u32 *rec = reinterpret_cast<u32 *>(o.packed) + 4 * i + 1;
+        if (with_winner) *rec = pack_status(done, turn, winner);
+        else *reinterpret_cast<unsigned short *>(rec) = (unsigned short)pack_status(done, turn, 0);
+    }
+    if (o.done) o.done[i] = (uint8_t)done;
+    if (o.player_turn) o.player_turn[i] = (int8_t)turn;
+    if (with_winner && o.winner) o.winner[i] = (int8_t)winner;
+}
+
 // ---------------------------------------------------------------------------- reset
 template <int S>
 __global__ void __launch_bounds__(OTH_BLOCK) k_reset(oth_state s, i64 B, u64 seed, i64 base, int init_rand,
@@ -740,9 +771,8 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_observe(oth_state s, i64 B, int f
     bool zero_obs = false;
     if (active) {
         load_env<S>(e, s, i, B);
-        if (out.done) out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
-        if (out.player_turn) out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
-        if (out.winner) out.winner[i] = (int8_t)meta_winner(e.meta);
+        put_status(out, i, (e.meta & OTH_META_TERMINATED) ? 1 : 0, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1,
+                   meta_winner(e.meta), true);
         zero_obs = (flags & OTH_F_ZERO_IF_TERMINATED) && (e.meta & OTH_META_TERMINATED);
     }
     emit_dense<S>(e, active, zero_obs, false, flags, out, i - (threadIdx.x & 31), B, stage[threadIdx.x >> 5]);
@@ -762,11 +792,79 @@ struct StepParams {
     PhiloxKeys keys;     // philox_round_keys(seed), filled by the launcher
 };
 
+// 8x8 headline writer: the producer parks each 64-bit plane as FOUR words of nibbles-in-bytes in even / odd order
+// (lo even, lo odd, hi even, hi odd: 4 LOP3 + 2 SHF, no byte permutes -- 12 ALU-pipe instructions fewer per env than
+// nibble_bytes for the three planes); the consumer's byte address of nibble n = 4*part + j is then
+// (part>>1)*8 + (part&1)*2 + (j&1)*4 + (j>>1): still one per-lane base plus compile-time immediates.
+OTH_DEV uint4 nibble_bytes_eo(u64 x) {
+    const u32 lo = (u32)x, hi = (u32)(x >> 32);
+    return make_uint4(lo & 0x0F0F0F0Fu, (lo >> 4) & 0x0F0F0F0Fu, hi & 0x0F0F0F0Fu, (hi >> 4) & 0x0F0F0F0Fu);
+}
+template <bool HAS_NEG>
+OTH_DEV void fast8_full_eo(void *base, i64 env0, const uint4 *pos_rows, const uint4 *neg_rows, int lane) {
+    const u32 lane_off = (u32)((lane >> 2) * 16 + ((lane >> 1) & 1) * 8 + (lane & 1) * 2);
+    const u32 src = (u32)__cvta_generic_to_shared(pos_rows) + lane_off;
+    const u32 nsrc = (u32)__cvta_generic_to_shared(neg_rows) + lane_off;
+    char *dst = reinterpret_cast<char *>(base) + env0 * (i64)64 + (lane >> 2) * 64 + (lane & 3) * 16;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        u32 w[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int imm = k * 128 + (j & 1) * 4 + (j >> 1);
+            w[j] = spread4(lds_u8(src + imm));
+            if (HAS_NEG) w[j] = spread4(lds_u8(nsrc + imm)) * 0xFFu + w[j];
+        }
+        *reinterpret_cast<uint4 *>(dst + k * (8 * 64)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+// The headline output set with everything decided at compile time (oth_step dispatches here when it applies):
+// int8 `board` observation + dense legal mask, full warps only; S == 8 uses the even/odd nibble stage, the other
+// even sizes the slab writer.
 template <int S>
-__global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
+OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outputs &out, i64 warp_env0, WarpStage<S> &st) {
+    constexpr int W = Geo<S>::W;
+    static_assert((S * S) % 4 == 0, "fast path: even board sizes");
+    const int lane = threadIdx.x & 31;
+    const bool tw = e.meta & OTH_META_TURN_WHITE;
+    const BB<W> z = bb_zero<W>();
+    const BB<W> pos = bb_select(zero, z, bb_select(tw, e.white, e.black));     // othello.py:363-369
+    const BB<W> neg = bb_select(zero, z, bb_select(tw, e.black, e.white));
+    const BB<W> lg = bb_select(zero, z, e.legal);
+    if constexpr (S == 8) {
+        st.nib[NIB_POS0][lane][0] = nibble_bytes_eo(pos.w[0]);
+        st.nib[NIB_NEG0][lane][0] = nibble_bytes_eo(neg.w[0]);
+        st.nib[NIB_MASK][lane][0] = nibble_bytes_eo(lg.w[0]);
+        __syncwarp();
+        fast8_full_eo<true>(out.obs, warp_env0, &st.nib[NIB_POS0][0][0], &st.nib[NIB_NEG0][0][0], lane);
+        fast8_full_eo<false>(out.legal_mask, warp_env0, &st.nib[NIB_MASK][0][0], &st.nib[NIB_MASK][0][0], lane);
+        __syncwarp();
+    } else {
+        static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
+        unsigned char *slab = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
+        slab_expand<S, true>(slab, lane, pos, neg);
+        __syncwarp();
+        slab_copy<S>(slab, out.obs, warp_env0, lane);
+        __syncwarp();
+        slab_expand<S, false>(slab, lane, lg, lg);
+        __syncwarp();
+        slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
+        __syncwarp();
+    }
+}
+
+#ifndef OTH_STEP8_MIN_CTAS
+#define OTH_STEP8_MIN_CTAS 1    // resident CTAs per SM the 8x8 fast kernel is compiled for (8: register cap 64)
+#endif
+// SRC: OTH_ACT_* at compile time.  FAST: B is a multiple of the CTA size, the scalars go to out.packed only, and
+// the dense outputs are the int8 `board` observation + legal mask (even S) -- no per-output null checks, no
+// ragged-warp handling, no layout dispatch.  Everything else runs the general instantiation.
+template <int S, int SRC, bool FAST>
+__global__ void __launch_bounds__(OTH_BLOCK, (FAST && S == 8) ? OTH_STEP8_MIN_CTAS : 1) k_step(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
-    const bool active = i < p.B;
+    const bool active = FAST || i < p.B;
     EnvRegs<S> e = empty_env<S>();
     bool zero_obs = false;
     if (active) {
@@ -775,14 +873,15 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
         r.reward = 0; r.done = 1; r.winner = 0; r.action = -1;
         if (e.meta & OTH_META_TERMINATED) {
             zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
+            r.winner = meta_winner(e.meta);                    // its result stays readable (env.winner, othello.py:240)
         } else {
             i64 action = -1;
             const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
-            if (opening || p.action_source == OTH_ACT_RANDOM) {
+            if (opening || SRC == OTH_ACT_RANDOM) {
                 action = random_pick<S>(e.legal, philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
                 e.ctr++;
                 if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
-            } else if (p.action_source == OTH_ACT_GREEDY) {
+            } else if (SRC == OTH_ACT_GREEDY) {
                 const bool wm = e.meta & OTH_META_TURN_WHITE;
                 action = greedy_pick<S>(bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal);
             } else {
@@ -792,13 +891,10 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
             if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.keys, p.base + i, p.init_rand);
             store_env<S>(e, p.st, i, p.B);
         }
-        if (p.out.reward) p.out.reward[i] = (float)r.reward;
-        if (p.out.done) p.out.done[i] = (uint8_t)r.done;
-        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
-        if (p.out.winner) p.out.winner[i] = (int8_t)r.winner;
-        if (p.out.actions_out) p.out.actions_out[i] = r.action;
+        put_step_scalars<FAST>(p.out, i, r.reward, r.done, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1, r.winner, r.action);
     }
-    emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+    if constexpr (FAST) emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
+    else emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
 }
 
 // ------------------------------------------------------------------------- self-play
@@ -907,8 +1003,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_selfplay(SelfPlayParams p) {
         }
         p.sp.phase[i] = (uint8_t)ph;
         need = !(ph & OTH_SP_EMITTED);
-        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
-        if (p.out.done) p.out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
+        put_status(p.out, i, (e.meta & OTH_META_TERMINATED) ? 1 : 0, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1, 0, false);
     }
     const u32 nb = __ballot_sync(0xFFFFFFFFu, need);
     if ((threadIdx.x & 31) == 0 && nb != 0u && p.need_count != nullptr) atomicAdd(p.need_count, __popc(nb));
@@ -1061,8 +1156,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_teacher_student(TeacherStudentPar
         const bool need = !(ph & OTH_TS_EMITTED);
         need_w = need && (e.meta & OTH_META_TURN_WHITE);
         need_b = need && !(e.meta & OTH_META_TURN_WHITE);
-        if (p.out.player_turn) p.out.player_turn[i] = (e.meta & OTH_META_TURN_WHITE) ? 1 : -1;
-        if (p.out.done) p.out.done[i] = (e.meta & OTH_META_TERMINATED) ? 1 : 0;
+        put_status(p.out, i, (e.meta & OTH_META_TERMINATED) ? 1 : 0, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1, 0, false);
     }
     const u32 nb = __ballot_sync(0xFFFFFFFFu, need_b), nw = __ballot_sync(0xFFFFFFFFu, need_w);
     if ((threadIdx.x & 31) == 0 && p.need_count != nullptr) {
@@ -1379,10 +1473,24 @@ struct SizeLaunch {
         k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
         return cudaGetLastError();
     }
+    template <int SRC>
+    static void step_src(const StepParams &p, cudaStream_t q) {
+        const oth_outputs &o = p.out;
+        bool fast = false;
+        if constexpr ((S * S) % 4 == 0) {
+            fast = p.B % OTH_BLOCK == 0 && o.packed != nullptr && o.obs != nullptr && o.legal_mask != nullptr &&
+                   o.obs_layout == OTH_OBS_BOARD && o.obs_dtype == OTH_DTYPE_I8 && !o.reward && !o.done &&
+                   !o.player_turn && !o.winner && !o.actions_out;
+            if (fast) k_step<S, SRC, true><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        }
+        if (!fast) k_step<S, SRC, false><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+    }
     static cudaError_t step(const StepParams &p0, cudaStream_t q) {
         StepParams p = p0;
         p.keys = philox_round_keys(p.seed);
-        k_step<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        if (p.action_source == OTH_ACT_RANDOM) step_src<OTH_ACT_RANDOM>(p, q);
+        else if (p.action_source == OTH_ACT_GREEDY) step_src<OTH_ACT_GREEDY>(p, q);
+        else step_src<OTH_ACT_EXTERNAL>(p, q);
         return cudaGetLastError();
     }
     static cudaError_t policy(oth_state s, i64 B, int kind, int depth, u64 seed, u64 counter, i64 base, i64 *out,

@@ -119,12 +119,16 @@ class VecOthelloEnv(object):
             self.obs = torch.zeros(shape, dtype=obs_dtype, device=dev)
         self._mask_u8 = torch.zeros((B, N), dtype=torch.uint8, device=dev) if with_legal_mask else None
         self.legal_mask = self._mask_u8.view(torch.bool) if with_legal_mask else None
-        self.reward = torch.zeros((B,), dtype=torch.float32, device=dev)
-        self._done_u8 = torch.ones((B,), dtype=torch.uint8, device=dev)
+        # the five per-env scalars live in ONE 16-byte record per env (oth_outputs.packed: one store per env instead
+        # of five); reward / done / player_turn / winner / actions_taken are strided views of it
+        self._packed = torch.zeros((B, 16), dtype=torch.uint8, device=dev)
+        self._packed[:, 4] = 1                                                # done until the first reset()
+        self.reward = self._packed.view(torch.float32)[:, 0]
+        self._done_u8 = self._packed[:, 4]
         self.done = self._done_u8.view(torch.bool)
-        self.player_turn = torch.zeros((B,), dtype=torch.int8, device=dev)
-        self.winner = torch.zeros((B,), dtype=torch.int8, device=dev)
-        self.actions_taken = torch.zeros((B,), dtype=torch.int64, device=dev)
+        self.player_turn = self._packed.view(torch.int8)[:, 5]
+        self.winner = self._packed.view(torch.int8)[:, 6]
+        self.actions_taken = self._packed.view(torch.int64)[:, 1]
         self._policy_counter = 0
         self._host = None
         self._c_state = None
@@ -146,15 +150,13 @@ class VecOthelloEnv(object):
                 | (_cabi.F_LEGACY_SINGLE_MOVE_PLANE if self.legacy_single_move_plane else 0))
 
     def _outputs(self, with_scalars=True):
-        key = bool(with_scalars)
-        if key not in self._c_out:
-            self._c_out[key] = _cabi.OthOutputs(
-                _cabi.ptr(self.obs), _cabi.ptr(self._mask_u8),
-                _cabi.ptr(self.reward) if with_scalars else None,
-                _cabi.ptr(self._done_u8), _cabi.ptr(self.player_turn), _cabi.ptr(self.winner),
-                _cabi.ptr(self.actions_taken) if with_scalars else None,
-                _LAYOUTS[self.obs_layout], _DTYPES[self.obs_dtype])
-        return self._c_out[key]
+        """oth_outputs of this env.  The scalars always travel through the packed record: oth_step writes all of it,
+        oth_observe (with_scalars=False at the call sites) only its status bytes."""
+        if "out" not in self._c_out:
+            self._c_out["out"] = _cabi.OthOutputs(
+                _cabi.ptr(self.obs), _cabi.ptr(self._mask_u8), None, None, None, None, None,
+                _LAYOUTS[self.obs_layout], _DTYPES[self.obs_dtype], _cabi.ptr(self._packed))
+        return self._c_out["out"]
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
@@ -167,7 +169,10 @@ class VecOthelloEnv(object):
 
     # ------------------------------------------------------------------ Gym-like API
     def seed(self, seed):
-        """SimpleOthelloEnv.seed (othello.py:53-58): new stream key; takes effect at the next reset()."""
+        """SimpleOthelloEnv.seed (othello.py:53-58): new stream key and rewound stream position, effective AT ONCE:
+        the key is an argument of every later step() (opening plies, fused random policy, auto-reset budgets), so
+        games in progress continue on the new stream.  Call reset() next for a fresh, reproducible batch (the
+        reference swaps its RandomState object the same way, mid-game included)."""
         self.seed_value = int(seed) & 0xFFFFFFFFFFFFFFFF
         self._ctr.zero_()
 
@@ -247,7 +252,10 @@ class VecOthelloEnv(object):
                 "actions_dev": torch.empty((self.num_envs,), dtype=torch.int64, device=self.device),
                 "obs": pin(self.obs) if self.obs is not None else None,
                 "mask": pin(self._mask_u8) if self._mask_u8 is not None else None,
-                "reward": pin(self.reward), "done": pin(self._done_u8),
+                "reward": torch.empty((self.num_envs,), dtype=torch.float32, pin_memory=True),
+                "done": torch.empty((self.num_envs,), dtype=torch.uint8, pin_memory=True),
+                "reward_dev": torch.empty((self.num_envs,), dtype=torch.float32, device=self.device),
+                "done_dev": torch.empty((self.num_envs,), dtype=torch.uint8, device=self.device),
             }
         h = self._host
         if actions_host.dtype == torch.int64:
@@ -266,8 +274,10 @@ class VecOthelloEnv(object):
             h["obs"].copy_(self.obs, non_blocking=True)
         if h["mask"] is not None:
             h["mask"].copy_(self._mask_u8, non_blocking=True)
-        h["reward"].copy_(self.reward, non_blocking=True)
-        h["done"].copy_(self._done_u8, non_blocking=True)
+        h["reward_dev"].copy_(self.reward)                  # gather the strided views on the device: 5 B per env
+        h["done_dev"].copy_(self._done_u8)                  # cross PCIe, not the 16-byte records
+        h["reward"].copy_(h["reward_dev"], non_blocking=True)
+        h["done"].copy_(h["done_dev"], non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return h["obs"], h["reward"], h["done"], h["mask"]
 

@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define OTH_ABI_VERSION 1
+#define OTH_ABI_VERSION 2
 #define OTH_MIN_BOARD_SIZE 4   /* othello.py:230 clamps to >= 4 */
 #define OTH_MAX_BOARD_SIZE 16   /* 256 cells = 4 words per colour; actions fit the int16 traces */
 
@@ -110,6 +110,11 @@ typedef struct oth_outputs {
     int64_t *actions_out;  /* [B] the action actually applied (after policy / random-opening override) */
     int32_t obs_layout;    /* OTH_OBS_* */
     int32_t obs_dtype;     /* OTH_DTYPE_* */
+    void    *packed;       /* [B] 16-byte records (16-byte aligned), or NULL: the five per-env scalars in ONE store --
+                              bytes 0-3 float reward | 4 uint8 done | 5 int8 player_turn | 6 int8 winner | 7 zero |
+                              8-15 int64 action applied.  oth_step writes the whole record; oth_observe and the protocol
+                              calls, which do not produce a reward / action, write bytes 4-7 only (the protocol calls
+                              bytes 4-5).  Written in addition to whichever of the separate arrays are not NULL. */
 } oth_outputs;
 
 typedef struct oth_policy_spec {

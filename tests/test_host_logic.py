@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol():
         assert getattr(lib, name) is not None
     lib.oth_abi_version.restype = ctypes.c_int
     lib.oth_words_per_board.restype = ctypes.c_int
-    assert lib.oth_abi_version() == 1                       # no GPU needed for these two
+    assert lib.oth_abi_version() == 2                       # no GPU needed for these two
     assert [lib.oth_words_per_board(s) for s in (3, 4, 8, 9, 11, 12, 13, 14, 16, 17)] == [0, 1, 1, 2, 2, 3, 3, 4, 4, 0]
 
 
@@ -53,8 +53,8 @@ def test_header_constants_match_python_binding():
              "OTH_META_WINNER_SHIFT": _cabi.META_WINNER_SHIFT}
     for k, v in pairs.items():
         assert defs[k] == v, k
-    # struct layouts: 5 pointers / 7 pointers + 2 int32
-    assert ctypes.sizeof(_cabi.OthState) == 40 and ctypes.sizeof(_cabi.OthOutputs) == 64
+    # struct layouts: 5 pointers / 7 pointers + 2 int32 + the packed-record pointer
+    assert ctypes.sizeof(_cabi.OthState) == 40 and ctypes.sizeof(_cabi.OthOutputs) == 72
     assert ctypes.sizeof(_cabi.OthPolicySpec) == 8
 
 
