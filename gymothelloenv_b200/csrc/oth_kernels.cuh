@@ -855,7 +855,7 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
 }
 
 #ifndef OTH_STEP8_MIN_CTAS
-#define OTH_STEP8_MIN_CTAS 1    // resident CTAs per SM the 8x8 fast kernel is compiled for (8: register cap 64)
+#define OTH_STEP8_MIN_CTAS 0    // min resident CTAs per SM the 8x8 fast kernel is compiled for (0: compiler default; 8: register cap 64)
 #endif
 // SRC: OTH_ACT_* at compile time.  FAST: B is a multiple of the CTA size, the scalars go to out.packed only, and
 // the dense outputs are the int8 `board` observation + legal mask (even S) -- no per-output null checks, no
