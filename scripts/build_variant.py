@@ -26,3 +26,5 @@ b.OBJ_DIR = os.path.join(b.LIB_DIR, "obj")
 b.LIB_PATH = os.path.join(b.LIB_DIR, "libothello_b200.so")
 b.NVCC_FLAGS = b.NVCC_FLAGS + flags
 print(b.build(force=True, verbose=True, only_sizes=sizes, reuse_obj_dir=main_obj))
+import shutil  # noqa: E402
+shutil.rmtree(b.OBJ_DIR)   # the snapshot sent to the GPU box is size-limited; the variant only needs its .so
