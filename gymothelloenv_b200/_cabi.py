@@ -51,8 +51,9 @@ EXPORTED_SYMBOLS = (
     "oth_abi_version", "oth_last_error", "oth_words_per_board", "oth_reset", "oth_observe", "oth_step",
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
     "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
-    "oth_epsilon_greedy", "oth_ts_new_game", "oth_ts_begin", "oth_ts_advance",
+    "oth_epsilon_greedy", "oth_ts_new_game", "oth_ts_begin", "oth_ts_advance", "oth_rollout_noalloc",
 )
+NOALLOC_MAX_GAMES = 1 << 21
 
 
 class OthState(C.Structure):
@@ -129,6 +130,9 @@ def load():
     L.oth_rollout.argtypes = [C.c_int64, C.c_int, C.c_int, OthPolicySpec, OthPolicySpec, C.c_int, C.c_int,
                               C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_int, C.c_void_p]
+    L.oth_rollout_noalloc.restype = C.c_int
+    L.oth_rollout_noalloc.argtypes = [C.c_int64, C.c_int, C.c_int, OthPolicySpec, OthPolicySpec, C.c_int, C.c_int,
+                                      C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p]
     L.oth_set_board.restype = C.c_int
     L.oth_set_board.argtypes = [OthState, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                 C.c_void_p]

@@ -3,6 +3,7 @@
 // in oth_kernels.cuh.  No torch types, no global mutable state, never throws.
 #include <cstdio>
 #include <cstring>
+#include <pthread.h>
 #include "oth_kernels.cuh"
 
 #define OTH_API extern "C" __attribute__((visibility("default")))
@@ -143,6 +144,95 @@ OTH_API int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec bl
     p.game_result = game_result; p.game_plies = game_plies; p.game_counts = game_counts; p.trace = trace;
     p.trace_stride = trace_stride;
     return cuda_result(ops->rollout(p, (cudaStream_t)stream), "oth_rollout");
+}
+
+// ------------------------------------------------------------------------------------------------
+// oth_rollout_noalloc: the fused tournament for callers that cannot allocate device memory (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  The rollout kernels write their per-game records
+// (winner int8, plies int16) into a FILE-SCOPE device array instead of caller buffers and a reduction kernel folds
+// the records into the caller's 4-word tally.  Nothing here calls cudaMalloc / cudaFree or an allocating routine.
+//   - every GPU that loads the library holds the array (OTH_NOALLOC_MAX_GAMES * 3 bytes = 6 MiB) until exit;
+//   - all calls on one device share it: two calls whose kernels overlap on the GPU (different streams) race;
+//   - nothing in it has to start at zero: the rollout writes records [0, games) and the reduction reads exactly
+//     that range, so the contents left by the previous call are never observed.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: the device address is fetched with
+// cudaGetSymbolAddress once per device (that device current) and handed to the kernels as a plain pointer.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[(size_t)OTH_NOALLOC_MAX_GAMES * 3];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static void *g_noalloc_addr[NOALLOC_MAX_DEVICES];      // written once per device; readers take the same lock
+static pthread_mutex_t g_noalloc_lock = PTHREAD_MUTEX_INITIALIZER;
+
+static int noalloc_scratch(unsigned char **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_result(e, "oth_rollout_noalloc: cudaGetDevice");
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(OTH_ERR_BAD_ARG, "oth_rollout_noalloc: device index out of range");
+    pthread_mutex_lock(&g_noalloc_lock);
+    void *addr = g_noalloc_addr[dev];
+    if (addr == nullptr) {
+        e = cudaGetSymbolAddress(&addr, g_noalloc_scratch);       // `dev` is current: its copy of the array
+        if (e == cudaSuccess) g_noalloc_addr[dev] = addr;
+    }
+    pthread_mutex_unlock(&g_noalloc_lock);
+    if (e != cudaSuccess) return cuda_result(e, "oth_rollout_noalloc: cudaGetSymbolAddress");
+    *out = (unsigned char *)addr;
+    return 0;
+}
+
+// records -> tally[0..3] += {black wins, draws, white wins, plies}: block-reduced, 4 atomics per block
+__global__ void __launch_bounds__(256) k_noalloc_reduce(const int16_t *plies, const int8_t *result, i64 games,
+                                                        unsigned long long *tally) {
+    __shared__ u32 part[4][8];
+    u32 c[4] = {0u, 0u, 0u, 0u};
+    for (i64 g = (i64)blockIdx.x * blockDim.x + threadIdx.x; g < games; g += (i64)gridDim.x * blockDim.x) {
+        const int w = result[g];
+        c[0] += w < 0; c[1] += w == 0; c[2] += w > 0; c[3] += (u32)plies[g];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xFFFFFFFFu, c[k], o);
+        if ((threadIdx.x & 31) == 0) part[k][threadIdx.x >> 5] = c[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        unsigned long long s = 0;
+        for (int w = 0; w < 8; w++) s += part[threadIdx.x][w];
+        if (s) atomicAdd(&tally[threadIdx.x], s);
+    }
+}
+
+OTH_API int oth_rollout_noalloc(int64_t B, int board_size, int flags, oth_policy_spec black, oth_policy_spec white,
+                                int init_rand_steps, int games_per_env, uint64_t seed, int64_t env_id_base,
+                                unsigned long long *tally, void *stream) {
+    const OthSizeOps *ops = ops_for(board_size);
+    if (ops == nullptr) return fail(OTH_ERR_BAD_BOARD_SIZE, "board_size unsupported");
+    if (B < 0 || games_per_env < 0) return fail(OTH_ERR_BAD_ARG, "negative count");
+    if (int rc = check_spec(black)) return rc;
+    if (int rc = check_spec(white)) return rc;
+    if (init_rand_steps < 0 || init_rand_steps > 254) return fail(OTH_ERR_BAD_ARG, "init_rand_steps must be in 0..254");
+    if (tally == nullptr) return fail(OTH_ERR_NULL_POINTER, "tally is null");
+    if (B > OTH_NOALLOC_MAX_GAMES || games_per_env > OTH_NOALLOC_MAX_GAMES ||
+        B * (int64_t)games_per_env > OTH_NOALLOC_MAX_GAMES) {
+        snprintf(g_err, sizeof(g_err), "oth_rollout_noalloc: %lld games exceed the static scratch (max %d games per call); "
+                 "split the call or use oth_rollout", (long long)B * games_per_env, OTH_NOALLOC_MAX_GAMES);
+        return OTH_ERR_BAD_ARG;
+    }
+    if (B == 0 || games_per_env == 0) return 0;
+    unsigned char *scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    const i64 games = B * (i64)games_per_env;
+    int16_t *plies = reinterpret_cast<int16_t *>(scratch);                                   // [MAX] int16
+    int8_t *result = reinterpret_cast<int8_t *>(scratch + (size_t)OTH_NOALLOC_MAX_GAMES * 2);   // [MAX] int8
+    RolloutParams p;
+    p.B = B; p.flags = flags | OTH_F_SUDDEN_DEATH; p.black = black; p.white = white; p.init_rand = init_rand_steps;
+    p.games_per_env = games_per_env; p.seed = seed; p.base = env_id_base; p.tally = nullptr;
+    p.game_result = result; p.game_plies = plies; p.game_counts = nullptr; p.trace = nullptr; p.trace_stride = 0;
+    if (int rc = cuda_result(ops->rollout(p, (cudaStream_t)stream), "oth_rollout_noalloc (rollout)")) return rc;
+    const unsigned blocks = (unsigned)((games + 255) / 256 < 592 ? (games + 255) / 256 : 592);   // <= 4 per SM
+    k_noalloc_reduce<<<blocks, 256, 0, (cudaStream_t)stream>>>(plies, result, games, tally);
+    return cuda_result(cudaGetLastError(), "oth_rollout_noalloc (reduce)");
 }
 
 OTH_API int oth_set_board(oth_state st, int64_t B, int board_size, const int8_t *cells, const int8_t *perspective,

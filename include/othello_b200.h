@@ -170,6 +170,20 @@ int oth_rollout(int64_t B, int board_size, int flags, oth_policy_spec black, oth
                 unsigned long long *tally, int8_t *game_result, int16_t *game_plies, int16_t *game_counts,
                 int16_t *trace, int trace_stride, void *stream);
 
+/* oth_rollout for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same games, same arguments and the same tally += {black wins, draws, white wins, plies} as oth_rollout (without
+ * its optional per-game records), but the per-game records the reduction needs live in a file-scope device array of
+ * the library -- OTH_NOALLOC_MAX_GAMES * 3 bytes (6 MiB) held by every GPU that loads the library until exit -- and
+ * the call performs no cudaMalloc / cudaFree or any allocating routine.  B * games_per_env above
+ * OTH_NOALLOC_MAX_GAMES is refused with OTH_ERR_BAD_ARG (split the call, or use oth_rollout).  All calls on a device
+ * share the array: calls whose kernels overlap on the GPU (different streams) race; calls on one stream are safe.
+ * The tally is accumulated by a deterministic-input reduction (block partial sums, 4 atomics per block). */
+#define OTH_NOALLOC_MAX_GAMES (1 << 21)
+int oth_rollout_noalloc(int64_t B, int board_size, int flags, oth_policy_spec black, oth_policy_spec white,
+                        int init_rand_steps, int games_per_env, uint64_t seed, int64_t env_id_base,
+                        unsigned long long *tally, void *stream);
+
 /* set_board_state + set_player_turn (othello.py:380-389,464-466): dense cells [B][S*S]
  * int8 seen from perspective[i] (+1: WHITE=+1, -1: negated), new turn[i] (-1/+1).
  * recompute_legal != 0 refreshes the cached list (set_player_turn); 0 keeps it
