@@ -861,7 +861,7 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
 // the dense outputs are the int8 `board` observation + legal mask (even S) -- no per-output null checks, no
 // ragged-warp handling, no layout dispatch.  Everything else runs the general instantiation.
 template <int S, int SRC, bool FAST>
-__global__ void __launch_bounds__(OTH_BLOCK, (FAST && S == 8) ? OTH_STEP8_MIN_CTAS : 1) k_step(StepParams p) {
+__global__ void __launch_bounds__(OTH_BLOCK, (FAST && S == 8) ? OTH_STEP8_MIN_CTAS : 0) k_step(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
     const bool active = FAST || i < p.B;

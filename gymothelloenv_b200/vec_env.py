@@ -240,12 +240,17 @@ class VecOthelloEnv(object):
                 "actions": self.actions_taken}
 
     # ------------------------------------------------------------------ host-buffer path
-    def step_host(self, actions_host):
+    def step_host(self, actions_host, packed=False):
         """The same step through HOST buffers: pinned H2D of the actions, kernel, pinned D2H
         of obs / legal mask / reward / done.  `actions_host`: pinned integer CPU tensor [B]; int64 like the
         device API, or a narrower signed type (int16 holds every action of a 16x16 board and -1): it then
         crosses PCIe at its own width and is widened on the device.
-        Returns CPU tensors (pinned, reused across calls)."""
+        Returns CPU tensors (pinned, reused across calls).
+
+        packed=True: instead of the dense obs + mask (2*S*S bytes per env) the call returns the step's result in its
+        packed form -- a dict of pinned CPU tensors {black, white, legal: int64 (W,B) bitboards; reward f32 (B,);
+        done u8 (B,); player_turn i8 (B,)} = 24*W + 6 bytes per env (30 instead of 133 at 8x8) -- for host consumers
+        that expand lazily (`expand_packed_host` does it for any subset of envs).  The dense path stays the default."""
         if self._host is None:
             pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True)   # noqa: E731
             self._host = {
@@ -270,6 +275,24 @@ class VecOthelloEnv(object):
             h["actions_dev"].copy_(h[key])                       # widened on the device
         self._host_action_bytes = actions_host.element_size()
         self.step(h["actions_dev"])
+        self._host_packed = bool(packed)
+        if packed:
+            if "black" not in h:
+                for name in ("black", "white", "legal"):
+                    h[name] = torch.empty((self.words, self.num_envs), dtype=torch.int64, pin_memory=True)
+                h["turn"] = torch.empty((self.num_envs,), dtype=torch.int8, pin_memory=True)
+                h["turn_dev"] = torch.empty((self.num_envs,), dtype=torch.int8, device=self.device)
+            h["reward_dev"].copy_(self.reward)
+            h["done_dev"].copy_(self._done_u8)
+            h["turn_dev"].copy_(self.player_turn)
+            for name in ("black", "white", "legal"):
+                h[name].copy_(getattr(self, "_" + name), non_blocking=True)
+            h["reward"].copy_(h["reward_dev"], non_blocking=True)
+            h["done"].copy_(h["done_dev"], non_blocking=True)
+            h["turn"].copy_(h["turn_dev"], non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+            return {"black": h["black"], "white": h["white"], "legal": h["legal"], "reward": h["reward"],
+                    "done": h["done"], "player_turn": h["turn"]}
         if h["obs"] is not None:
             h["obs"].copy_(self.obs, non_blocking=True)
         if h["mask"] is not None:
@@ -284,11 +307,31 @@ class VecOthelloEnv(object):
     def host_bytes_per_step(self):
         """(h2d, d2h) bytes moved by one step_host() call (h2d at the width of the last actions_host passed)."""
         d2h = self.reward.numel() * 4 + self._done_u8.numel()
+        if getattr(self, "_host_packed", False):
+            return (self.num_envs * getattr(self, "_host_action_bytes", 8),
+                    d2h + self.num_envs * (24 * self.words + 1))
         if self.obs is not None:
             d2h += self.obs.numel() * self.obs.element_size()
         if self._mask_u8 is not None:
             d2h += self._mask_u8.numel()
         return self.num_envs * getattr(self, "_host_action_bytes", 8), d2h
+
+    def expand_packed_host(self, packed, index=None):
+        """Host-side (numpy) expansion of step_host(packed=True) results for the envs in `index` (all when None):
+        -> (obs int8 (n,S,S): mover +1 / opponent -1, othello.py:363-369; legal_mask bool (n,S*S))."""
+        import numpy as np
+        S, N = self.board_size, self.num_cells
+        idx = slice(None) if index is None else np.asarray(index)
+        cells = np.arange(N)
+        word, bit = cells >> 6, (cells & 63).astype(np.uint64)
+
+        def bits(t):
+            w = t.numpy().view(np.uint64)[:, idx]                       # (W, n)
+            return ((w[word, :] >> bit[:, None]) & np.uint64(1)).T.astype(np.int8)   # (n, N)
+        black, white, legal = bits(packed["black"]), bits(packed["white"]), bits(packed["legal"])
+        turn = packed["player_turn"].numpy()[idx].astype(np.int8)[:, None]
+        obs = (white - black) * turn
+        return obs.reshape(-1, S, S), legal.astype(bool)
 
     # ------------------------------------------------------------------ accessors
     def observe(self, layout=None, dtype=None, out=None):

@@ -1,9 +1,10 @@
 """TEST INFRASTRUCTURE -- import shim for the live Python reference.
 
-Only usable in the build container (``/root/reference`` does not exist on the GPU
-box).  It is used by ``tests/golden/make_golden.py`` to generate the committed golden
-vectors and by ``oracle/validate_against_reference.py`` to differential-test the C
-oracle.  Nothing in the product package imports this file.
+In the build container it imports the reference from ``/root/reference`` (golden generators under
+``tests/golden/``, ``oracle/validate_against_reference.py``).  On the GPU box, where that tree does not exist,
+``load_reference()`` imports the bytecode build of the same three modules that ``oracle/make_ref.py`` left in
+``oracle/_ref/`` -- that is how ``bench.py``'s CPU legs time the reference's own code.  Nothing in the product
+package imports this file.
 
 The reference's ``othello.py:3-7`` imports ``gym``/``pyglet`` (absent here) but only
 uses ``gym.Env`` as a base class and ``spaces.Discrete/Box`` as shape metadata
@@ -73,10 +74,26 @@ def _install_stubs():
         sys.modules["ppo"] = ppo
 
 
-def load_reference():
-    """Returns (othello, simple_policies, util) modules of the live reference."""
+def prebuilt_available():
+    from oracle import make_ref
+    return make_ref.available()
+
+
+def load_reference(prefer_prebuilt=False):
+    """Returns (othello, simple_policies, util) modules of the reference: the live tree when it is present, else
+    (or when prefer_prebuilt) the bytecode build in oracle/_ref/."""
+    if (prefer_prebuilt or not reference_available()) and prebuilt_available():
+        from oracle import make_ref
+        _install_stubs()
+        if make_ref.OUT not in sys.path:
+            sys.path.insert(0, make_ref.OUT)
+        import othello  # noqa
+        import simple_policies  # noqa
+        import util  # noqa
+        assert os.path.dirname(os.path.abspath(othello.__file__)) == os.path.abspath(make_ref.OUT), othello.__file__
+        return othello, simple_policies, util
     if not reference_available():
-        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+        raise RuntimeError("reference not available: no tree at %s and no build in oracle/_ref/" % REFERENCE_ROOT)
     _install_stubs()
     # The product package has same-named modules (othello.py, simple_policies.py,
     # util.py) *inside* gymothelloenv_b200/, never at top level, so these top-level

@@ -152,3 +152,18 @@ def random_playout_steps(board_size, seed, seconds):
         dt = time.perf_counter() - t0
         if dt >= seconds:
             return steps, dt
+
+
+def make_state(env):
+    """util.py:48-74 on the port's env: planes [black, white, turn, legal]; the legal plane stays empty unless the
+    mover has >= 2 moves (util.py:55-56).  Only the CPU-baseline fallback uses it (cost model of configs[3])."""
+    n = env.size
+    obs = np.array(env.observation(), copy=True)
+    legal = np.zeros((n, n))
+    if len(env.moves) > 1:
+        idx = np.array(env.moves)
+        legal[idx // n, idx % n] = 1
+    mine, theirs = (obs == 1).astype(float), (obs == -1).astype(float)
+    if env.turn == BLACK:
+        return np.stack([mine, theirs, np.zeros((n, n)), legal])
+    return np.stack([theirs, mine, np.ones((n, n)), legal])

@@ -14,9 +14,8 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
 
-def pytest_collection_modifyitems(config, items):
-    """GPU tests must never silently pass on a box without CUDA: they fail loudly."""
-    return
+# GPU tests are never skipped on a box without CUDA: every product constructor raises OthelloB200Error there, so a
+# `-m gpu` run without a device fails loudly (tests/test_host_logic.py::test_product_fails_loudly_without_cuda).
 
 
 @pytest.fixture(scope="session")

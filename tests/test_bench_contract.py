@@ -30,10 +30,27 @@ def test_reference_arm_prints_one_contract_line():
     assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 1 and d["value"] > 0
     assert d["config"]["workload"].startswith("8x8 lockstep batch")
     cb = d["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
+    from oracle import make_ref
+    assert cb["kind"] == ("reference" if make_ref.available() else "port")
     e = d["e2e"]
     assert e["value"] == d["value"] and e["unit"] == d["unit"]
     assert e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
+
+
+@pytest.mark.parametrize("config,unit", [("sizes", "env_steps/s"), ("ppo_feed", "env_steps/s"),
+                                         ("tournament", "games/s")])
+def test_reference_arm_of_the_other_configs(config, unit):
+    from oracle import make_ref
+    if config == "tournament" and not make_ref.available():
+        pytest.skip("the reference's policies are needed (oracle/_ref not built)")
+    r = _run(["--impl", "reference", "--config", config, "--steps", "1", "--warmup", "0", "--cpu-seconds", "1"])
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == unit and d["value"] > 0 and d["e2e"]["value"] == d["value"]
+    assert d["cpu_baseline"]["cores"] >= 1 and "configs[" in d["config"]["workload"]
 
 
 def test_reference_arm_is_silent_on_other_ranks():
