@@ -16,10 +16,8 @@ def run(args):
     from oracle import cpu_arms
     t_all = time.perf_counter()
     arms = cpu_arms.CpuArms()
-    K = max(1, min(args.steps, 5))                 # bounded: each "step" = one sample of >= 10 s per worker
-    per = max(1.0, min(60.0, args.cpu_seconds))       # default 12 s per worker and sample (>= 10 s)
-    if args.steps * per > 180:                     # keep the whole arm within a few minutes
-        K = max(1, int(180 // per))
+    per = max(1.0, min(60.0, args.cpu_seconds))    # default 12 s per worker and sample (>= 10 s)
+    K = max(1, min(args.steps, 5, int(120 // per)))   # bounded: a "step" = one sample; the arm ends within minutes
     cfg = args.config
     samples, extra = [], {}
     for _ in range(min(1, args.warmup)):           # one short untimed pass
