@@ -85,12 +85,7 @@ def load_reference(prefer_prebuilt=False):
     if (prefer_prebuilt or not reference_available()) and prebuilt_available():
         from oracle import make_ref
         _install_stubs()
-        if make_ref.OUT not in sys.path:
-            sys.path.insert(0, make_ref.OUT)
-        import othello  # noqa
-        import simple_policies  # noqa
-        import util  # noqa
-        assert os.path.dirname(os.path.abspath(othello.__file__)) == os.path.abspath(make_ref.OUT), othello.__file__
+        othello, simple_policies, util = make_ref.load_modules()
         return othello, simple_policies, util
     if not reference_available():
         raise RuntimeError("reference not available: no tree at %s and no build in oracle/_ref/" % REFERENCE_ROOT)
