@@ -9,10 +9,10 @@ from . import _cabi
 from ._cabi import OthelloB200Error
 from .vec_env import VecOthelloEnv, shard_range
 from .envs import Envs, PPOEnvs, PPOTeacherStudentEnvs
-from .sampling import masked_categorical, LegalMoveSampler, epsilon_greedy, EpsilonGreedy
+from .sampling import masked_categorical, LegalMoveSampler, epsilon_greedy, EpsilonGreedy, evaluate_actions, ChoiceStore
 
 BLACK_DISK = -1   # othello.py:10
 NO_DISK = 0       # othello.py:11
 WHITE_DISK = 1    # othello.py:12
 
-__all__ = ["VecOthelloEnv", "Envs", "PPOEnvs", "PPOTeacherStudentEnvs", "masked_categorical", "LegalMoveSampler", "epsilon_greedy", "EpsilonGreedy", "OthelloB200Error", "shard_range", "BLACK_DISK", "NO_DISK", "WHITE_DISK"]
+__all__ = ["VecOthelloEnv", "Envs", "PPOEnvs", "PPOTeacherStudentEnvs", "masked_categorical", "LegalMoveSampler", "evaluate_actions", "ChoiceStore", "epsilon_greedy", "EpsilonGreedy", "OthelloB200Error", "shard_range", "BLACK_DISK", "NO_DISK", "WHITE_DISK"]

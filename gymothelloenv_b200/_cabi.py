@@ -52,6 +52,7 @@ EXPORTED_SYMBOLS = (
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
     "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
     "oth_epsilon_greedy", "oth_ts_new_game", "oth_ts_begin", "oth_ts_advance", "oth_rollout_noalloc",
+    "oth_masked_logprob_forward", "oth_masked_logprob_backward",
 )
 NOALLOC_MAX_GAMES = 1 << 21
 
@@ -153,6 +154,12 @@ def load():
     L.oth_masked_categorical.restype = C.c_int
     L.oth_masked_categorical.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_uint64,
                                          C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oth_masked_logprob_forward.restype = C.c_int
+    L.oth_masked_logprob_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]
+    L.oth_masked_logprob_backward.restype = C.c_int
+    L.oth_masked_logprob_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_void_p, C.c_void_p]
     L.oth_epsilon_greedy.restype = C.c_int
     L.oth_epsilon_greedy.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_uint64, C.c_uint64,
                                      C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

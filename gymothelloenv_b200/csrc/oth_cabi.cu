@@ -490,6 +490,156 @@ OTH_API int oth_masked_categorical(const float *logits, const uint64_t *legal, i
     return cuda_result(cudaGetLastError(), "oth_masked_categorical");
 }
 
+// ---- evaluate_actions for the PPO update (model.py:156-198, algo/ppo.py:51-66), differentiable ------------------
+// forward:  logp[i]    = log softmax(logits[i][choices_i])[action_i], 0 when the action is not a legal choice or there
+//                        is no choice (model.py:167-168 returns the constant 0 there: no gradient either)
+//           entropy[i] = entropy of the FULL S*S-way softmax(logits[i]) -- the reference takes dist.entropy() of the
+//                        unmasked distribution (model.py:159,178)
+// backward: grad_logits[i][a] = g_logp[i] * (1[a == action_i] - p_legal[i][a]) on legal a (0 elsewhere, all-zero row
+//                               when logp was the constant 0)  +  g_ent[i] * dH/dx_a,  dH/dx_a = -p_a (log p_a + H)
+// One warp per env, lane l holds cells l, l+32, ...; everything is recomputed in the backward (4*S*S bytes per env).
+struct CatRow {
+    float x[CAT_MAXK];
+    bool ok[CAT_MAXK], in[CAT_MAXK];
+    float m_all, s_all, m_leg, s_leg;
+    bool any_legal;
+};
+OTH_DEV void cat_row_load(CatRow &r, const float *logits, const u64 *legal, i64 B, int N, i64 env, int lane) {
+    const float NEG_INF = __int_as_float(0xFF800000u);
+    const int K = (N + 31) >> 5;
+    r.m_all = NEG_INF; r.m_leg = NEG_INF;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const int a = 32 * k + lane;
+        r.in[k] = k < K && a < N;
+        r.ok[k] = false; r.x[k] = NEG_INF;
+        if (r.in[k]) {
+            r.x[k] = logits[env * N + a];
+            r.ok[k] = (legal[(i64)(a >> 6) * B + env] >> (a & 63)) & 1ull;
+            r.m_all = fmaxf(r.m_all, r.x[k]);
+            if (r.ok[k]) r.m_leg = fmaxf(r.m_leg, r.x[k]);
+        }
+    }
+    u32 any = 0;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) any |= __ballot_sync(0xFFFFFFFFu, r.ok[k]);
+    r.any_legal = any != 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        r.m_all = fmaxf(r.m_all, __shfl_xor_sync(0xFFFFFFFFu, r.m_all, o));
+        r.m_leg = fmaxf(r.m_leg, __shfl_xor_sync(0xFFFFFFFFu, r.m_leg, o));
+    }
+    r.s_all = 0.f; r.s_leg = 0.f;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        if (r.in[k]) r.s_all += expf(r.x[k] - r.m_all);
+        if (r.ok[k]) r.s_leg += expf(r.x[k] - r.m_leg);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        r.s_all += __shfl_xor_sync(0xFFFFFFFFu, r.s_all, o);
+        r.s_leg += __shfl_xor_sync(0xFFFFFFFFu, r.s_leg, o);
+    }
+}
+// is `a` one of the env's legal choices?  (warp-uniform result)
+OTH_DEV bool cat_action_legal(const CatRow &r, i64 a, int N) {
+    if ((u64)a >= (u64)N) return false;
+    bool g = false;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        const bool v = __shfl_sync(0xFFFFFFFFu, (int)r.ok[k], (int)a & 31);
+        if (((int)a >> 5) == k) g = v;
+    }
+    return g;
+}
+// entropy of the full distribution: H = logZ - sum_a p_a x_a
+OTH_DEV float cat_entropy(const CatRow &r) {
+    float px = 0.f;
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++)
+        if (r.in[k]) px += expf(r.x[k] - r.m_all) * r.x[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) px += __shfl_xor_sync(0xFFFFFFFFu, px, o);
+    return r.m_all + logf(r.s_all) - px / r.s_all;
+}
+
+__global__ void __launch_bounds__(128) k_masked_logprob_fwd(const float *logits, const u64 *legal, i64 B, int N,
+                                                            const i64 *actions, float *logp_out, float *entropy_out) {
+    const i64 env = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= B) return;
+    CatRow r;
+    cat_row_load(r, logits, legal, B, N, env, lane);
+    const i64 a = actions[env];
+    const bool legal_choice = r.any_legal && cat_action_legal(r, a, N);
+    float xa = 0.f;
+    if (legal_choice) xa = logits[env * N + a];
+    const float H = entropy_out != nullptr ? cat_entropy(r) : 0.f;
+    if (lane == 0) {
+        if (logp_out) logp_out[env] = legal_choice ? (xa - r.m_leg - logf(r.s_leg)) : 0.f;
+        if (entropy_out) entropy_out[env] = H;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_masked_logprob_bwd(const float *logits, const u64 *legal, i64 B, int N,
+                                                            const i64 *actions, const float *g_logp, const float *g_ent,
+                                                            float *grad_logits) {
+    const i64 env = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (env >= B) return;
+    CatRow r;
+    cat_row_load(r, logits, legal, B, N, env, lane);
+    const i64 a = actions[env];
+    const bool legal_choice = r.any_legal && cat_action_legal(r, a, N);
+    const float gl = (g_logp != nullptr && legal_choice) ? g_logp[env] : 0.f;
+    const float ge = g_ent != nullptr ? g_ent[env] : 0.f;
+    float H = 0.f, logZ = 0.f;
+    if (g_ent != nullptr) { H = cat_entropy(r); logZ = r.m_all + logf(r.s_all); }
+#pragma unroll
+    for (int k = 0; k < CAT_MAXK; k++) {
+        if (!r.in[k]) continue;
+        const int c = 32 * k + lane;
+        float g = 0.f;
+        if (r.ok[k]) g = gl * ((c == (int)a ? 1.f : 0.f) - expf(r.x[k] - r.m_leg) / r.s_leg);
+        if (g_ent != nullptr) {
+            const float lp = r.x[k] - logZ;
+            g += ge * (-expf(lp) * (lp + H));
+        }
+        grad_logits[env * N + c] = g;
+    }
+}
+
+static int check_logprob_args(const float *logits, const uint64_t *legal, int64_t B, int board_size, const int64_t *actions) {
+    if (ops_for(board_size) == nullptr) return fail(OTH_ERR_BAD_BOARD_SIZE, "board_size unsupported");
+    if (B < 0) return fail(OTH_ERR_BAD_ARG, "negative count");
+    if (logits == nullptr || legal == nullptr || actions == nullptr) return fail(OTH_ERR_NULL_POINTER, "logits / legal / actions is null");
+    if (board_size * board_size > 32 * CAT_MAXK) return fail(OTH_ERR_BAD_BOARD_SIZE, "board too large for the sampler");
+    return 0;
+}
+
+OTH_API int oth_masked_logprob_forward(const float *logits, const uint64_t *legal, int64_t B, int board_size,
+                                       const int64_t *actions, float *logp_out, float *entropy_out, void *stream) {
+    if (int rc = check_logprob_args(logits, legal, B, board_size, actions)) return rc;
+    if (logp_out == nullptr && entropy_out == nullptr) return fail(OTH_ERR_NULL_POINTER, "no output requested");
+    if (B == 0) return 0;
+    const unsigned grid = (unsigned)((B * 32 + 127) / 128);
+    k_masked_logprob_fwd<<<grid, 128, 0, (cudaStream_t)stream>>>(logits, (const u64 *)legal, B, board_size * board_size,
+                                                                 (const i64 *)actions, logp_out, entropy_out);
+    return cuda_result(cudaGetLastError(), "oth_masked_logprob_forward");
+}
+
+OTH_API int oth_masked_logprob_backward(const float *logits, const uint64_t *legal, int64_t B, int board_size,
+                                        const int64_t *actions, const float *grad_logp, const float *grad_entropy,
+                                        float *grad_logits, void *stream) {
+    if (int rc = check_logprob_args(logits, legal, B, board_size, actions)) return rc;
+    if (grad_logits == nullptr) return fail(OTH_ERR_NULL_POINTER, "grad_logits is null");
+    if (B == 0) return 0;
+    const unsigned grid = (unsigned)((B * 32 + 127) / 128);
+    k_masked_logprob_bwd<<<grid, 128, 0, (cudaStream_t)stream>>>(logits, (const u64 *)legal, B, board_size * board_size,
+                                                                 (const i64 *)actions, grad_logp, grad_entropy, grad_logits);
+    return cuda_result(cudaGetLastError(), "oth_masked_logprob_backward");
+}
+
 // ---- epsilon-greedy over the legal moves (dqn.py:264-275,478-488) --------------------
 // One warp per env, lane l holds q of actions l, l+32, ...  Explore: the n-th set bit of the
 // legal bitset (= the n-th entry of the ascending possible_moves list).  Exploit: first argmax.

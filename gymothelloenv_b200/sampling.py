@@ -8,6 +8,11 @@ env) reads the learner's logits [B, S*S] and the env's legal-move BITSET (no den
 no lists) and returns the action and its log-probability under softmax(logits[legal]).
 Edge cases follow the reference: no legal move -> action 0, log-prob 0 (:71-73); in
 evaluate mode an action that is not a legal choice gets log-prob 0 (:172-173).
+
+``masked_categorical`` (sample / mode / evaluate) is the ROLLOUT side and carries no gradient.  The PPO update's
+``evaluate_actions`` (differentiated at ``algo/ppo.py:51-66``) is ``evaluate_actions`` below: an autograd function
+with a hand-written backward kernel plus the full-distribution entropy; ``ChoiceStore`` keeps the rollout's
+`choices` as device bitsets (``storage.py:19,48-57,133-145``).
 """
 import ctypes as C
 
@@ -52,6 +57,112 @@ def masked_categorical(logits, legal_words, board_size, mode="sample", actions=N
     return out_a, out_lp
 
 
+def _stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+class _MaskedLogProb(torch.autograd.Function):
+    """(log-prob of `actions` under softmax over the legal subset, entropy of the full distribution) with a
+    hand-written backward kernel (oth_masked_logprob_forward / _backward)."""
+
+    @staticmethod
+    def forward(ctx, logits, legal_words, actions, board_size):
+        lib = _cabi.load()
+        B = logits.shape[0]
+        x = logits.detach().to(torch.float32).contiguous()
+        logp = torch.empty((B,), dtype=torch.float32, device=x.device)
+        ent = torch.empty((B,), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _cabi.check(lib.oth_masked_logprob_forward(_cabi.ptr(x), _cabi.ptr(legal_words), B, int(board_size),
+                                                       _cabi.ptr(actions), _cabi.ptr(logp), _cabi.ptr(ent),
+                                                       _stream(x.device)), "oth_masked_logprob_forward")
+        ctx.save_for_backward(x, legal_words, actions)
+        ctx.board_size = int(board_size)
+        ctx.in_dtype = logits.dtype
+        return logp, ent
+
+    @staticmethod
+    def backward(ctx, g_logp, g_ent):
+        x, legal_words, actions = ctx.saved_tensors
+        lib = _cabi.load()
+        B = x.shape[0]
+        grad = torch.empty_like(x)
+        gl = None if g_logp is None else g_logp.to(torch.float32).contiguous()
+        ge = None if g_ent is None else g_ent.to(torch.float32).contiguous()
+        with torch.cuda.device(x.device):
+            _cabi.check(lib.oth_masked_logprob_backward(_cabi.ptr(x), _cabi.ptr(legal_words), B, ctx.board_size,
+                                                        _cabi.ptr(actions), _cabi.ptr(gl), _cabi.ptr(ge),
+                                                        _cabi.ptr(grad), _stream(x.device)),
+                        "oth_masked_logprob_backward")
+        return grad.to(ctx.in_dtype), None, None, None
+
+
+def evaluate_actions(logits, legal_words, actions, board_size):
+    """The distribution part of ``Policy.evaluate_actions`` (model.py:156-198) for a whole minibatch, differentiable
+    w.r.t. ``logits``: -> (action_log_probs float32 [B, 1], dist_entropy scalar).
+
+    logits float32 CUDA [B, S*S] (the actor head's output, requires_grad); legal_words int64 CUDA [W, B]: the
+    `choices` of every sample as bitsets (``ChoiceStore.gather``); actions int64 [B] or [B, 1].
+    action_log_probs[i] is the log-probability of actions[i] under softmax(logits[i][choices_i]); it is the
+    constant 0 -- with zero gradient -- when actions[i] is not among the choices or there are none (:167-168).
+    dist_entropy is the mean entropy of the FULL S*S-way distribution, as the reference computes it (:159,178)."""
+    if not (isinstance(logits, torch.Tensor) and logits.is_cuda):
+        raise _cabi.OthelloB200Error("evaluate_actions needs CUDA tensors (no CPU path)")
+    S = int(board_size)
+    B = logits.shape[0]
+    if logits.dim() != 2 or logits.shape[1] != S * S:
+        raise ValueError("logits must be [B, board_size**2]")
+    legal_words = legal_words.contiguous()
+    if legal_words.dtype != torch.int64 or tuple(legal_words.shape) != (_cabi.words_per_board(S), B):
+        raise ValueError("legal_words must be int64 [W, B]")
+    a = actions.to(device=logits.device, dtype=torch.int64).reshape(-1).contiguous()
+    if a.numel() != B:
+        raise ValueError("actions must have one entry per sample")
+    logp, ent = _MaskedLogProb.apply(logits, legal_words, a, S)
+    return logp.unsqueeze(1), ent.mean()
+
+
+class ChoiceStore(object):
+    """The `choices` of a PPO rollout on the device: int64 bitsets [T, W, B] instead of RolloutStorage's list of lists
+    (storage.py:19 `self.choices`, :48-57 `insert`), and the minibatch gather of :133-145 as ONE indexed copy."""
+
+    def __init__(self, num_steps, num_envs, board_size, device):
+        self.num_steps, self.num_envs, self.board_size = int(num_steps), int(num_envs), int(board_size)
+        self.words = _cabi.words_per_board(self.board_size)
+        self.data = torch.zeros((self.num_steps, self.words, self.num_envs), dtype=torch.int64, device=device)
+        self.step = 0
+
+    def insert(self, legal_words):
+        """storage.py:56: the legal set [W, B] of the state the step's action was chosen in (None = no choices)."""
+        if legal_words is None:
+            self.data[self.step].zero_()
+        else:
+            self.data[self.step].copy_(legal_words)
+        self.step = (self.step + 1) % self.num_steps                     # storage.py:64
+
+    def gather(self, indices):
+        """choices_batch for flat sample indices i = t * num_envs + b (the order of `.view(-1, ...)` in
+        feed_forward_generator, storage.py:127-145) -> int64 [W, len(indices)], ready for evaluate_actions."""
+        idx = torch.as_tensor(indices, dtype=torch.int64, device=self.data.device)
+        flat = self.data.permute(1, 0, 2).reshape(self.words, self.num_steps * self.num_envs)
+        return flat.index_select(1, idx).contiguous()
+
+    def as_lists(self, indices):
+        """The reference's representation (lists of ascending action ids), for tests and debugging."""
+        words = self.gather(indices).cpu().tolist()
+        out = []
+        for j in range(len(words[0])):
+            moves = []
+            for w in range(self.words):
+                v = words[w][j] & 0xFFFFFFFFFFFFFFFF
+                while v:
+                    low = v & -v
+                    moves.append(w * 64 + low.bit_length() - 1)
+                    v ^= low
+            out.append(moves)
+        return out
+
+
 class LegalMoveSampler(object):
     """Stateful convenience over masked_categorical for one VecOthelloEnv: every sample() call
     uses the next Philox counter, so a rollout is reproducible from (seed, env ids)."""
@@ -71,8 +182,14 @@ class LegalMoveSampler(object):
         return masked_categorical(logits, self.env._legal, self.env.board_size, "mode")
 
     def log_probs(self, logits, actions, legal_words=None):
+        """Log-probabilities of `actions` WITHOUT a gradient path (rollout bookkeeping).  The PPO update uses
+        `evaluate_actions`, which is differentiable."""
         lw = self.env._legal if legal_words is None else legal_words
         return masked_categorical(logits, lw, self.env.board_size, "evaluate", actions=actions)[1]
+
+    def evaluate_actions(self, logits, actions, legal_words=None):
+        lw = self.env._legal if legal_words is None else legal_words
+        return evaluate_actions(logits, lw, actions, self.env.board_size)
 
 
 def epsilon_greedy(q_values, legal_words, board_size, epsilon, seed=0, counter=0, env_id_base=0):

@@ -328,6 +328,22 @@ int oth_masked_categorical(const float *logits, const uint64_t *legal, int64_t B
                            const int64_t *actions_in, uint64_t seed, uint64_t counter, int64_t env_id_base,
                            int64_t *actions_out, float *logp_out, void *stream);
 
+/* Policy.evaluate_actions for the PPO update (a2c_ppo_acktr/model.py:156-198, differentiated by algo/ppo.py:51-66),
+ * batched and DIFFERENTIABLE.  legal = the `choices` of every sample as bitsets [W][B] (storage.py:19,48-57 keeps
+ * python lists).  forward:
+ *   logp_out[i]    = log softmax(logits[i][choices_i])[actions[i]]; the constant 0 when actions[i] is not one of the
+ *                    choices or there are none (model.py:167-168) -- such rows get no gradient
+ *   entropy_out[i] = entropy of the FULL S*S-way softmax(logits[i]) (model.py:159,178 uses the unmasked dist);
+ *                    the caller averages it (`dist.entropy().mean()`).  Either output may be NULL.
+ * backward: grad_logits[i][a] = grad_logp[i] * (1[a == actions[i]] - p_choices_i[a]) on the choices, 0 elsewhere
+ *                              + grad_entropy[i] * dH_i/dlogits[i][a]       (either incoming gradient may be NULL)
+ * float32; the backward recomputes the forward (4*S*S bytes per sample), nothing is saved between the calls. */
+int oth_masked_logprob_forward(const float *logits, const uint64_t *legal, int64_t B, int board_size,
+                               const int64_t *actions, float *logp_out, float *entropy_out, void *stream);
+int oth_masked_logprob_backward(const float *logits, const uint64_t *legal, int64_t B, int board_size,
+                                const int64_t *actions, const float *grad_logp, const float *grad_entropy,
+                                float *grad_logits, void *stream);
+
 /* Epsilon-greedy over the legal moves, the DQN agent's action choice (dqn.py:264-275 get_action,
  * :478-488 get_action_at_test): with probability epsilon (`epsilon >= u`, u uniform in [0,1) as at dqn.py:266)
  * a uniformly random entry of the ascending legal list, else the legal move with the largest q value, FIRST
