@@ -378,6 +378,9 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
 #endif
 
 // ---- multi-word boards: flips by carry propagation -------------------------------------
+#ifndef OTH_RAY_PROGRESSION
+#define OTH_RAY_PROGRESSION 1   // 0: round-1 ray masks (variable whole-board shift of a per-direction pattern), for A/B
+#endif
 // whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
 template <int W> OTH_DEV BB<W> bb_shl_var(const BB<W> &x, int a) {
     const int q = a >> 6, b = a & 63;
@@ -426,6 +429,45 @@ template <int W> OTH_DEV BB<W> ray_flips(const BB<W> &m, const BB<W> &P, const B
     BB_FOR(i) r.w[i] = closed ? (m.w[i] & O.w[i] & ~t.w[i]) : 0ull;   // ray cells the carry rippled through
     return r;
 }
+// Ray masks without a variable whole-board shift.  The carry trick only needs the ray's cells to be the arithmetic
+// progression a + D, a + 2D, ... (it may run on past the ray's end: the ripple stops at the first progression cell
+// that is not an inner-column opponent disc, and padding bits hold neither colour), so
+//     ray(a, D) = (PROG_D << (a mod D)) & above(a)
+// PROG_D = every D-th bit of the W words (compile time); a mod D <= 16 < 32, so the shift is ONE funnel shift per
+// 32-bit half (2W SHF, no selects); above(a) = the bits higher than a, shared by the three rays of a half.  This
+// replaced bb_shl_var (a 64-bit variable shift per word plus a W x W select network): S = 12 2139 -> see profiles/.
+constexpr u64 geo_word_prog(int D, int wi) {
+    u64 m = 0;
+    for (int b = 0; b < 64; b++)
+        if ((wi * 64 + b) % D == 0) m |= 1ull << b;
+    return m;
+}
+template <int D, int WI> struct GeoProgWord { static constexpr u64 v = geo_word_prog(D, WI); };
+template <int D, int W> OTH_DEV BB<W> geo_prog() {
+    BB<W> r;
+    r.w[0] = GeoProgWord<D, 0>::v;
+    if constexpr (W > 1) r.w[1] = GeoProgWord<D, 1>::v;
+    if constexpr (W > 2) r.w[2] = GeoProgWord<D, 2>::v;
+    if constexpr (W > 3) r.w[3] = GeoProgWord<D, 3>::v;
+    return r;
+}
+// whole-board shift towards higher bit indices by 0 <= r < 32
+template <int W> OTH_DEV BB<W> bb_shl_lt32(const BB<W> &x, int r) {
+    u32 h[2 * W], o[2 * W];
+    BB_FOR(i) { h[2 * i] = (u32)x.w[i]; h[2 * i + 1] = (u32)(x.w[i] >> 32); }
+#pragma unroll
+    for (int j = 0; j < 2 * W; j++) o[j] = __funnelshift_l(j > 0 ? h[j > 0 ? j - 1 : 0] : 0u, h[j], r);
+    BB<W> y;
+    BB_FOR(i) y.w[i] = (u64)o[2 * i] | ((u64)o[2 * i + 1] << 32);
+    return y;
+}
+// bits strictly above the single bit mv (mv == 0: none)
+template <int W> OTH_DEV BB<W> bb_above(const BB<W> &mv) {
+    const BB<W> below = bb_sub<W>(mv, bb_one<W>(1ull));
+    BB<W> r;
+    BB_FOR(i) r.w[i] = ~(mv.w[i] | below.w[i]);
+    return r;
+}
 // the four rays towards higher bit indices from cell a (mv = its bit): east needs no ray mask -- the
 // carry out of mv<<1 ripples through the inner-column opponent run and lands on the cell behind it
 template <int S>
@@ -436,9 +478,16 @@ OTH_DEV BB<Geo<S>::W> flips_up(int a, const BB<Geo<S>::W> &mv, const BB<Geo<S>::
     const BB<W> sum = bb_add<W>(Oi, first);
     const BB<W> land = andnot(sum, Oi) & P;
     BB<W> f = bb_select(any(land), andnot(Oi, sum), bb_zero<W>());   // the discs the carry rippled through
+#if OTH_RAY_PROGRESSION
+    const BB<W> above = bb_above<W>(mv);
+    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S, W>(), a % S) & above, P, O);
+    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S + 1, W>(), a % (S + 1)) & above, P, Oi);
+    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S - 1, W>(), a % (S - 1)) & above, P, Oi);
+#else
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S>(), a), P, O);
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S + 1>(), a), P, Oi);
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S - 1>(), a), P, Oi);
+#endif
     return f;
 }
 
@@ -563,6 +612,21 @@ OTH_DEV u32 philox_draw(const PhiloxKeys &K, i64 gid, u32 stream, u32 ctr) {
     u32 k = ctr & 3u;
     return k == 0 ? b.v[0] : (k == 1 ? b.v[1] : (k == 2 ? b.v[2] : b.v[3]));
 }
+// Whole games in one kernel draw consecutive words of one stream: keep the 4-word block in registers and run the ten
+// rounds only when the draw index crosses a block boundary (every 4th draw).  Same stream, 1/4 of the Philox work.
+struct PhiloxCache {
+    Philox4 b;
+    u32 block;          // index of the cached block, 0xFFFFFFFF = none
+};
+OTH_DEV void philox_cache_reset(PhiloxCache &c) { c.block = 0xFFFFFFFFu; c.b.v[0] = c.b.v[1] = c.b.v[2] = c.b.v[3] = 0u; }
+OTH_DEV u32 philox_draw_cached(PhiloxCache &c, const PhiloxKeys &K, i64 gid, u32 stream, u32 ctr) {
+    if ((ctr >> 2) != c.block) {
+        c.b = philox4x32_10(ctr >> 2, stream, (u32)(u64)gid, (u32)((u64)gid >> 32), K);
+        c.block = ctr >> 2;
+    }
+    const u32 k = ctr & 3u;
+    return k == 0 ? c.b.v[0] : (k == 1 ? c.b.v[1] : (k == 2 ? c.b.v[2] : c.b.v[3]));
+}
 // uniform integer in [0, n) from 32 random bits (Lemire multiply-shift; bias <= n/2^32)
 OTH_DEV int bounded(u32 r, int n) { return (int)(((u64)r * (u64)(u32)n) >> 32); }
 
@@ -593,6 +657,21 @@ OTH_DEV void env_reset(EnvRegs<S> &e, const KEY &seed, i64 gid, int init_rand_st
         e.ctr++;
     }
     e.meta = (u32)budget << OTH_META_RANDMAX_SHIFT;   // turn = BLACK, not terminated, winner 0, cnt 0
+}
+
+// the same with the rollout kernels' cached Philox block
+template <int S>
+OTH_DEV void env_reset_cached(EnvRegs<S> &e, PhiloxCache &c, const PhiloxKeys &K, i64 gid, int init_rand_steps) {
+    e.black = geo_start_black<S>();
+    e.white = geo_start_white<S>();
+    e.legal = geo_start_legal<S>();
+    int half = init_rand_steps / 2;
+    int budget = 0;
+    if (half > 0) {
+        budget = 2 * bounded(philox_draw_cached(c, K, gid, OTH_STREAM_ENV, e.ctr), half + 1);
+        e.ctr++;
+    }
+    e.meta = (u32)budget << OTH_META_RANDMAX_SHIFT;
 }
 
 struct StepResult {

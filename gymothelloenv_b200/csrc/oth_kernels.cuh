@@ -8,6 +8,7 @@
 // 512 contiguous bytes (st.global.v4), instead of 32 strided 64-byte rows.
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include "oth_core.cuh"
 #include "oth_coop_search.cuh"
 
@@ -860,41 +861,80 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
 // SRC: OTH_ACT_* at compile time.  FAST: B is a multiple of the CTA size, the scalars go to out.packed only, and
 // the dense outputs are the int8 `board` observation + legal mask (even S) -- no per-output null checks, no
 // ragged-warp handling, no layout dispatch.  Everything else runs the general instantiation.
-template <int S, int SRC, bool FAST>
-__global__ void __launch_bounds__(OTH_BLOCK, (FAST && S == 8) ? OTH_STEP8_MIN_CTAS : 0) k_step(StepParams p) {
+// One env's step (policy / opening override -> rules -> auto-reset -> state store -> scalars): shared by the
+// one-tile general kernel and the multi-tile fast kernel.  `ext_action` = the caller's action for OTH_ACT_EXTERNAL.
+template <int S, int SRC, bool PACKED_ONLY>
+OTH_DEV void step_one_env(const StepParams &p, EnvRegs<S> &e, i64 i, i64 ext_action, bool &zero_obs) {
+    StepResult r;
+    r.reward = 0; r.done = 1; r.winner = 0; r.action = -1;
+    if (e.meta & OTH_META_TERMINATED) {
+        zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
+        r.winner = meta_winner(e.meta);                    // its result stays readable (env.winner, othello.py:240)
+    } else {
+        i64 action = -1;
+        const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
+        if (opening || SRC == OTH_ACT_RANDOM) {
+            action = random_pick<S>(e.legal, philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
+            e.ctr++;
+            if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
+        } else if (SRC == OTH_ACT_GREEDY) {
+            const bool wm = e.meta & OTH_META_TURN_WHITE;
+            action = greedy_pick<S>(bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal);
+        } else {
+            action = ext_action;
+        }
+        r = env_step<S>(e, action, p.flags);
+        if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.keys, p.base + i, p.init_rand);
+        store_env<S>(e, p.st, i, p.B);
+    }
+    put_step_scalars<PACKED_ONLY>(p.out, i, r.reward, r.done, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1, r.winner, r.action);
+}
+
+// SRC: OTH_ACT_* at compile time.  General kernel: one 128-env tile per CTA, any B, any output set.
+template <int S, int SRC>
+__global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
-    const bool active = FAST || i < p.B;
+    const bool active = i < p.B;
     EnvRegs<S> e = empty_env<S>();
     bool zero_obs = false;
     if (active) {
         load_env<S>(e, p.st, i, p.B);
-        StepResult r;
-        r.reward = 0; r.done = 1; r.winner = 0; r.action = -1;
-        if (e.meta & OTH_META_TERMINATED) {
-            zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
-            r.winner = meta_winner(e.meta);                    // its result stays readable (env.winner, othello.py:240)
-        } else {
-            i64 action = -1;
-            const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
-            if (opening || SRC == OTH_ACT_RANDOM) {
-                action = random_pick<S>(e.legal, philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
-                e.ctr++;
-                if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
-            } else if (SRC == OTH_ACT_GREEDY) {
-                const bool wm = e.meta & OTH_META_TURN_WHITE;
-                action = greedy_pick<S>(bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal);
-            } else {
-                action = p.actions[i];
-            }
-            r = env_step<S>(e, action, p.flags);
-            if (r.done && (p.flags & OTH_F_AUTO_RESET)) env_reset<S>(e, p.keys, p.base + i, p.init_rand);
-            store_env<S>(e, p.st, i, p.B);
-        }
-        put_step_scalars<FAST>(p.out, i, r.reward, r.done, (e.meta & OTH_META_TURN_WHITE) ? 1 : -1, r.winner, r.action);
+        step_one_env<S, SRC, false>(p, e, i, SRC == OTH_ACT_EXTERNAL ? p.actions[i] : (i64)-1, zero_obs);
     }
-    if constexpr (FAST) emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
-    else emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+    emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
+}
+
+// Fast kernel: B is a multiple of the CTA size, the scalars go to out.packed only and the dense outputs are the int8
+// `board` observation + legal mask (even S) -- no per-output null checks, no ragged-warp handling, no layout dispatch.
+// A CTA steps `tiles_per_cta` tiles of 128 envs (tile t = blockIdx.x + j * gridDim.x) and loads the NEXT tile's state
+// before it computes the current one: with one tile per CTA every warp sat out a DRAM round trip at its start
+// (`long_scoreboard` was the top stall, issue slots 31 % idle, profiles/r03a); now only a CTA's first tile does.
+// The launcher starts one CTA per resident slot, so every CTA is resident at once and tile counts differ by <= 1.
+template <int S, int SRC>
+__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_step_fast(StepParams p, int tiles_per_cta) {
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    const i64 ntiles = p.B / OTH_BLOCK;
+    i64 t = blockIdx.x;
+    EnvRegs<S> nxt = empty_env<S>();
+    i64 nact = -1;
+    if (t < ntiles) {
+        load_env<S>(nxt, p.st, t * OTH_BLOCK + threadIdx.x, p.B);
+        if (SRC == OTH_ACT_EXTERNAL) nact = p.actions[t * OTH_BLOCK + threadIdx.x];
+    }
+    for (int j = 0; j < tiles_per_cta && t < ntiles; j++, t += gridDim.x) {
+        const i64 i = t * OTH_BLOCK + threadIdx.x;
+        EnvRegs<S> e = nxt;
+        const i64 act = nact;
+        const i64 tn = t + gridDim.x;
+        if (j + 1 < tiles_per_cta && tn < ntiles) {          // in flight while this tile computes
+            load_env<S>(nxt, p.st, tn * OTH_BLOCK + threadIdx.x, p.B);
+            if (SRC == OTH_ACT_EXTERNAL) nact = p.actions[tn * OTH_BLOCK + threadIdx.x];
+        }
+        bool zero_obs = false;
+        step_one_env<S, SRC, true>(p, e, i, act, zero_obs);
+        emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
+    }
 }
 
 // ------------------------------------------------------------------------- self-play
@@ -1237,6 +1277,7 @@ struct RolloutParams {
     int16_t *game_counts;
     int16_t *trace;
     int trace_stride;
+    PhiloxKeys keys;     // philox_round_keys(seed), filled by the launcher
 };
 
 // Whole games in registers, one thread per game, every decision per thread (random / greedy pairings, and
@@ -1248,9 +1289,11 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
     if (i < p.B) {
         EnvRegs<S> e;
         e.ctr = 0;
+        PhiloxCache rng;
+        philox_cache_reset(rng);
         for (int g = 0; g < p.games_per_env; g++) {
             const i64 game = i * p.games_per_env + g;
-            env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+            env_reset_cached<S>(e, rng, p.keys, p.base + i, p.init_rand);
             int ply = 0;
             StepResult r;
             r.done = 0; r.winner = 0;
@@ -1260,7 +1303,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
                 const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);
                 int a;
                 if (opening || spec.kind == OTH_POLICY_RANDOM) {
-                    a = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                    a = random_pick<S>(e.legal, philox_draw_cached(rng, p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
                     e.ctr++;
                     if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
                 } else {
@@ -1309,9 +1352,11 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout_coop(RolloutParams p) {
     const bool in_range = i < p.B;
     u32 t_black = 0, t_draw = 0, t_white = 0, t_plies = 0;
     EnvRegs<S> e = empty_env<S>();
+    PhiloxCache rng;
+    philox_cache_reset(rng);
     for (int g = 0; g < p.games_per_env; g++) {
         const i64 game = i * p.games_per_env + g;
-        if (in_range) env_reset<S>(e, p.seed, p.base + i, p.init_rand);
+        if (in_range) env_reset_cached<S>(e, rng, p.keys, p.base + i, p.init_rand);
         int ply = 0;
         StepResult r;
         r.done = in_range ? 0 : 1; r.winner = 0; r.reward = 0; r.action = -1;
@@ -1325,7 +1370,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout_coop(RolloutParams p) {
             if (live) {
                 const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);
                 if (opening || spec.kind == OTH_POLICY_RANDOM) {
-                    a = random_pick<S>(e.legal, philox_draw(p.seed, p.base + i, OTH_STREAM_ENV, e.ctr));
+                    a = random_pick<S>(e.legal, philox_draw_cached(rng, p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
                     e.ctr++;
                     if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
                 } else if (W == 1 && spec.kind == OTH_POLICY_MAXIMIN && spec.depth >= 2 && any(e.legal)) {
@@ -1473,6 +1518,35 @@ struct SizeLaunch {
         k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
         return cudaGetLastError();
     }
+    // Grid of the fast kernel: one CTA per resident slot (SMs x resident CTAs per SM), every CTA strides over the
+    // tiles until they run out, so all CTAs are resident at once and their tile counts differ by at most one.
+    // OTH_STEP_TPC=n (development) caps the tiles per CTA instead (1 = one tile per CTA, the round-1 schedule).
+    template <int SRC>
+    static void fast_launch_shape(i64 ntiles, unsigned &grid, int &tiles_per_cta) {
+        static int slots = 0;                       // idempotent: racing threads compute the same value
+        static int forced = -1;
+        if (forced < 0) {
+            const char *v = getenv("OTH_STEP_TPC");
+            forced = v ? atoi(v) : 0;
+        }
+        if (forced <= 0 && slots == 0) {
+            int dev = 0, sms = 0, per_sm = 0;
+            if (cudaGetDevice(&dev) == cudaSuccess &&
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step_fast<S, SRC>, OTH_BLOCK, 0) == cudaSuccess &&
+                sms > 0 && per_sm > 0)
+                slots = sms * per_sm;
+            else
+                cudaGetLastError();
+        }
+        if (forced > 0 || slots == 0) {
+            tiles_per_cta = forced > 0 ? forced : 1;
+            grid = (unsigned)((ntiles + tiles_per_cta - 1) / tiles_per_cta);
+        } else {
+            tiles_per_cta = 0x7FFFFFFF;
+            grid = (unsigned)(ntiles < slots ? ntiles : slots);
+        }
+    }
     template <int SRC>
     static void step_src(const StepParams &p, cudaStream_t q) {
         const oth_outputs &o = p.out;
@@ -1481,9 +1555,14 @@ struct SizeLaunch {
             fast = p.B % OTH_BLOCK == 0 && o.packed != nullptr && o.obs != nullptr && o.legal_mask != nullptr &&
                    o.obs_layout == OTH_OBS_BOARD && o.obs_dtype == OTH_DTYPE_I8 && !o.reward && !o.done &&
                    !o.player_turn && !o.winner && !o.actions_out;
-            if (fast) k_step<S, SRC, true><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+            if (fast) {
+                unsigned grid;
+                int tpc;
+                fast_launch_shape<SRC>(p.B / OTH_BLOCK, grid, tpc);
+                k_step_fast<S, SRC><<<grid, OTH_BLOCK, 0, q>>>(p, tpc);
+            }
         }
-        if (!fast) k_step<S, SRC, false><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        if (!fast) k_step<S, SRC><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
     }
     static cudaError_t step(const StepParams &p0, cudaStream_t q) {
         StepParams p = p0;
@@ -1506,7 +1585,9 @@ struct SizeLaunch {
         k_policy<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, kind, depth, seed, counter, base, out);
         return cudaGetLastError();
     }
-    static cudaError_t rollout(const RolloutParams &p, cudaStream_t q) {
+    static cudaError_t rollout(const RolloutParams &p0, cudaStream_t q) {
+        RolloutParams p = p0;
+        p.keys = philox_round_keys(p.seed);
         const bool searches = (p.black.kind == OTH_POLICY_MAXIMIN && p.black.depth >= 2) ||
                               (p.white.kind == OTH_POLICY_MAXIMIN && p.white.depth >= 2);
         if (Geo<S>::W == 1 && searches && !(p.flags & OTH_F_SEARCH_PER_THREAD)) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
