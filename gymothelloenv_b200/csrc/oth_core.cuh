@@ -157,13 +157,16 @@ OTH_DEV BB<W> sh(const BB<W> &a) {
 // A 64-bit LEFT shift is one IMAD.SHL (low half, FMA pipe) + one SHF (high half, ALU pipe); a RIGHT shift is two
 // SHF on the ALU pipe, the binding unit of k_step.  legal1 therefore runs the downward directions as upward fills
 // on the bit-reversed boards (BREV is on the XU pipe) and reverses the union once.
-template <int D>
+// REACH = the longest run a fill must cover (S - 2): rounds reach 1, 2, 4, 6 cells; smaller boards stop earlier.
+template <int D, int REACH>
 OTH_DEV u64 fill_up1(u64 P, u64 m) {
     u64 f = m & (P << D);
     f |= m & (f << D);
-    const u64 pl = m & (m << D);
-    f |= pl & (f << (2 * D));
-    f |= pl & (f << (2 * D));
+    if constexpr (REACH > 2) {
+        const u64 pl = m & (m << D);
+        f |= pl & (f << (2 * D));
+        if constexpr (REACH > 4) f |= pl & (f << (2 * D));
+    }
     return f << D;
 }
 template <int S>
@@ -172,13 +175,13 @@ OTH_DEV u64 legal1(u64 P, u64 O) {
     const u64 Oi = O & GeoWord<S, 0>::inner;
     const u64 Pr = __brevll(P), Or = __brevll(O), Oir = __brevll(Oi);
     u64 up = (Oi + ((P << 1) & Oi)) & ~Oi;                 // east: carry through the opponent run
-    up |= fill_up1<S>(P, O);
-    up |= fill_up1<S - 1>(P, Oi);
-    up |= fill_up1<S + 1>(P, Oi);
+    up |= fill_up1<S, S - 2>(P, O);
+    up |= fill_up1<S - 1, S - 2>(P, Oi);
+    up |= fill_up1<S + 1, S - 2>(P, Oi);
     u64 dn = (Oir + ((Pr << 1) & Oir)) & ~Oir;             // west = east on the reversed board, and so on
-    dn |= fill_up1<S>(Pr, Or);
-    dn |= fill_up1<S - 1>(Pr, Oir);
-    dn |= fill_up1<S + 1>(Pr, Oir);
+    dn |= fill_up1<S, S - 2>(Pr, Or);
+    dn |= fill_up1<S - 1, S - 2>(Pr, Oir);
+    dn |= fill_up1<S + 1, S - 2>(Pr, Oir);
     const u64 moves = up | __brevll(dn);
     if constexpr (S == 8) return moves & ~(P | O);
     else return moves & ~(P | O) & GeoWord<S, 0>::full;

@@ -359,6 +359,11 @@ OTH_DEV void slab_expand(unsigned char *slab, int lane, const BB<Geo<S>::W> &pos
     constexpr int N = Geo<S>::N, G4 = N / 4;
     static_assert(N % 4 == 0, "slab writer: even board sizes only");
     u32 *dst = reinterpret_cast<u32 *>(slab + lane * N);
+    // S*S a multiple of 16 (S = 12): four words per 16-byte store -- a quarter-warp's 8 stores then fall into 8
+    // different 16-byte bank groups (lane stride 9 x 16 B), where the 32-bit stores were 4-way conflicted (lane
+    // stride 36 words), and there are 4x fewer store instructions.  S = 16 (stride 16 x 16 B) keeps 32-bit stores.
+    constexpr bool VEC = (N % 16 == 0) && ((N / 16) % 2 == 1);
+    u32 quad[4];
 #pragma unroll
     for (int r = 0; r < G4; r++) {
         const int k = r >> 4, sh = 4 * (r & 7);
@@ -369,7 +374,12 @@ OTH_DEV void slab_expand(unsigned char *slab, int lane, const BB<Geo<S>::W> &pos
             const u32 nh = hi ? (u32)(neg.w[k] >> 32) : (u32)neg.w[k];
             w = spread4((nh >> sh) & 0xFu) * 0xFFu + w;
         }
-        dst[r] = w;
+        if constexpr (VEC) {
+            quad[r & 3] = w;
+            if ((r & 3) == 3) reinterpret_cast<uint4 *>(dst)[r >> 2] = make_uint4(quad[0], quad[1], quad[2], quad[3]);
+        } else {
+            dst[r] = w;
+        }
     }
 }
 // Odd sizes (S*S % 4 != 0): lane e's S*S bytes start at byte e*S*S of the slab, `a` = that offset mod 4 past an
@@ -855,6 +865,12 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
     }
 }
 
+#ifndef OTH_STEP_TILES_PER_CTA
+#define OTH_STEP_TILES_PER_CTA 1   // default schedule of the fast step path (see SizeLaunch::fast_tiles_per_cta)
+#endif
+#ifndef OTH_STEP8_MULTI_MIN_CTAS
+#define OTH_STEP8_MULTI_MIN_CTAS 7   // the multi-tile 8x8 kernel is compiled for 7 resident CTAs per SM (72 registers)
+#endif
 #ifndef OTH_STEP8_MIN_CTAS
 #define OTH_STEP8_MIN_CTAS 0    // min resident CTAs per SM the 8x8 fast kernel is compiled for (0: compiler default; 8: register cap 64)
 #endif
@@ -905,32 +921,78 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
     emit_dense<S>(e, active, zero_obs, zero_obs, p.flags, p.out, i - (threadIdx.x & 31), p.B, stage[threadIdx.x >> 5]);
 }
 
-// Fast kernel: B is a multiple of the CTA size, the scalars go to out.packed only and the dense outputs are the int8
+// Fast kernels: B is a multiple of the CTA size, the scalars go to out.packed only and the dense outputs are the int8
 // `board` observation + legal mask (even S) -- no per-output null checks, no ragged-warp handling, no layout dispatch.
-// A CTA steps `tiles_per_cta` tiles of 128 envs (tile t = blockIdx.x + j * gridDim.x) and loads the NEXT tile's state
-// before it computes the current one: with one tile per CTA every warp sat out a DRAM round trip at its start
-// (`long_scoreboard` was the top stall, issue slots 31 % idle, profiles/r03a); now only a CTA's first tile does.
-// The launcher starts one CTA per resident slot, so every CTA is resident at once and tile counts differ by <= 1.
+// k_step_fast: one 128-env tile per CTA (the hardware's CTA scheduler staggers the CTAs' load / rules / store phases).
 template <int S, int SRC>
-__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_step_fast(StepParams p, int tiles_per_cta) {
+__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_step_fast(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
-    const i64 ntiles = p.B / OTH_BLOCK;
-    i64 t = blockIdx.x;
-    EnvRegs<S> nxt = empty_env<S>();
-    i64 nact = -1;
-    if (t < ntiles) {
-        load_env<S>(nxt, p.st, t * OTH_BLOCK + threadIdx.x, p.B);
-        if (SRC == OTH_ACT_EXTERNAL) nact = p.actions[t * OTH_BLOCK + threadIdx.x];
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    EnvRegs<S> e;
+    load_env<S>(e, p.st, i, p.B);
+    bool zero_obs = false;
+    step_one_env<S, SRC, true>(p, e, i, SRC == OTH_ACT_EXTERNAL ? p.actions[i] : (i64)-1, zero_obs);
+    emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
+}
+
+// k_step_fast_multi: a CTA steps `tiles_per_cta` tiles (tile t = blockIdx.x + j * gridDim.x).  With one tile per CTA
+// every warp sits out a DRAM round trip before its first instruction (`long_scoreboard` is the top stall, issue
+// slots ~30 % idle, profiles/r03a).  Here each thread copies the NEXT tile's state of "its" env into shared memory
+// with cp.async while it computes the current tile -- no registers are held across the tile (a register prefetch
+// cost 7 registers = one resident CTA per SM and lost more than it won, profiles/r03d) and, a thread reading back
+// only what it copied itself, no barrier is needed beyond cp.async.wait_group.  Two slots: the copy for tile j+1
+// must not land in the slot tile j is still read from.
+template <int S, bool WITH_ACTIONS>
+struct StateStage {
+    u64 bw[2][3 * Geo<S>::W][OTH_BLOCK];      // [slot][black words, white words, legal words][thread]
+    u32 mc[2][2][OTH_BLOCK];                  // [slot][meta, ctr][thread]
+    i64 act[2][WITH_ACTIONS ? OTH_BLOCK : 1];
+};
+OTH_DEV void cp_async8(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+OTH_DEV void cp_async4(void *smem, const void *gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+template <int S, int SRC>
+OTH_DEV void stage_state_async(StateStage<S, SRC == OTH_ACT_EXTERNAL> &sb, int slot, const StepParams &p, i64 i) {
+    constexpr int W = Geo<S>::W;
+    const int tid = threadIdx.x;
+    BB_FOR(k) {
+        cp_async8(&sb.bw[slot][k][tid], &p.st.black[k * p.B + i]);
+        cp_async8(&sb.bw[slot][W + k][tid], &p.st.white[k * p.B + i]);
+        cp_async8(&sb.bw[slot][2 * W + k][tid], &p.st.legal[k * p.B + i]);
     }
+    cp_async4(&sb.mc[slot][0][tid], &p.st.meta[i]);
+    cp_async4(&sb.mc[slot][1][tid], &p.st.ctr[i]);
+    if (SRC == OTH_ACT_EXTERNAL) cp_async8(&sb.act[slot][tid], &p.actions[i]);
+}
+template <int S, int SRC>
+__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MULTI_MIN_CTAS : 0) k_step_fast_multi(StepParams p, int tiles_per_cta) {
+    constexpr int W = Geo<S>::W;
+    __shared__ WarpStage<S> stage[OTH_WARPS];
+    __shared__ StateStage<S, SRC == OTH_ACT_EXTERNAL> sb;
+    const i64 ntiles = p.B / OTH_BLOCK;
+    const int tid = threadIdx.x;
+    i64 t = blockIdx.x;
+    if (t < ntiles) stage_state_async<S, SRC>(sb, 0, p, t * OTH_BLOCK + tid);
+    asm volatile("cp.async.commit_group;" ::: "memory");
     for (int j = 0; j < tiles_per_cta && t < ntiles; j++, t += gridDim.x) {
-        const i64 i = t * OTH_BLOCK + threadIdx.x;
-        EnvRegs<S> e = nxt;
-        const i64 act = nact;
+        const int slot = j & 1;
         const i64 tn = t + gridDim.x;
-        if (j + 1 < tiles_per_cta && tn < ntiles) {          // in flight while this tile computes
-            load_env<S>(nxt, p.st, tn * OTH_BLOCK + threadIdx.x, p.B);
-            if (SRC == OTH_ACT_EXTERNAL) nact = p.actions[tn * OTH_BLOCK + threadIdx.x];
+        if (j + 1 < tiles_per_cta && tn < ntiles) stage_state_async<S, SRC>(sb, slot ^ 1, p, tn * OTH_BLOCK + tid);
+        asm volatile("cp.async.commit_group;" ::: "memory");          // possibly empty: keeps the group count uniform
+        asm volatile("cp.async.wait_group 1;" ::: "memory");          // everything but the newest group: this tile is in
+        const i64 i = t * OTH_BLOCK + tid;
+        EnvRegs<S> e;
+        BB_FOR(k) {
+            e.black.w[k] = sb.bw[slot][k][tid];
+            e.white.w[k] = sb.bw[slot][W + k][tid];
+            e.legal.w[k] = sb.bw[slot][2 * W + k][tid];
         }
+        e.meta = sb.mc[slot][0][tid];
+        e.ctr = sb.mc[slot][1][tid];
+        const i64 act = SRC == OTH_ACT_EXTERNAL ? sb.act[slot][tid] : (i64)-1;
         bool zero_obs = false;
         step_one_env<S, SRC, true>(p, e, i, act, zero_obs);
         emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
@@ -1518,34 +1580,16 @@ struct SizeLaunch {
         k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
         return cudaGetLastError();
     }
-    // Grid of the fast kernel: one CTA per resident slot (SMs x resident CTAs per SM), every CTA strides over the
-    // tiles until they run out, so all CTAs are resident at once and their tile counts differ by at most one.
-    // OTH_STEP_TPC=n (development) caps the tiles per CTA instead (1 = one tile per CTA, the round-1 schedule).
-    template <int SRC>
-    static void fast_launch_shape(i64 ntiles, unsigned &grid, int &tiles_per_cta) {
-        static int slots = 0;                       // idempotent: racing threads compute the same value
-        static int forced = -1;
-        if (forced < 0) {
+    // tiles per CTA of the fast path: OTH_STEP_TPC (development A/B) or the measured default below.
+    // 1 = k_step_fast (one tile per CTA), n > 1 = k_step_fast_multi with n tiles per CTA and cp.async staging.
+    static int fast_tiles_per_cta() {
+        static int tpc = 0;                          // idempotent: racing threads compute the same value
+        if (tpc == 0) {
             const char *v = getenv("OTH_STEP_TPC");
-            forced = v ? atoi(v) : 0;
+            const int n = v ? atoi(v) : 0;
+            tpc = n > 0 ? n : OTH_STEP_TILES_PER_CTA;
         }
-        if (forced <= 0 && slots == 0) {
-            int dev = 0, sms = 0, per_sm = 0;
-            if (cudaGetDevice(&dev) == cudaSuccess &&
-                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step_fast<S, SRC>, OTH_BLOCK, 0) == cudaSuccess &&
-                sms > 0 && per_sm > 0)
-                slots = sms * per_sm;
-            else
-                cudaGetLastError();
-        }
-        if (forced > 0 || slots == 0) {
-            tiles_per_cta = forced > 0 ? forced : 1;
-            grid = (unsigned)((ntiles + tiles_per_cta - 1) / tiles_per_cta);
-        } else {
-            tiles_per_cta = 0x7FFFFFFF;
-            grid = (unsigned)(ntiles < slots ? ntiles : slots);
-        }
+        return tpc;
     }
     template <int SRC>
     static void step_src(const StepParams &p, cudaStream_t q) {
@@ -1556,10 +1600,14 @@ struct SizeLaunch {
                    o.obs_layout == OTH_OBS_BOARD && o.obs_dtype == OTH_DTYPE_I8 && !o.reward && !o.done &&
                    !o.player_turn && !o.winner && !o.actions_out;
             if (fast) {
-                unsigned grid;
-                int tpc;
-                fast_launch_shape<SRC>(p.B / OTH_BLOCK, grid, tpc);
-                k_step_fast<S, SRC><<<grid, OTH_BLOCK, 0, q>>>(p, tpc);
+                const i64 ntiles = p.B / OTH_BLOCK;
+                const int tpc = fast_tiles_per_cta();
+                bool multi = false;
+                if constexpr (Geo<S>::W == 1) {          // the staged state of multi-word boards does not fit 48 KB
+                    multi = tpc > 1 && ntiles >= 4 * tpc;
+                    if (multi) k_step_fast_multi<S, SRC><<<(unsigned)((ntiles + tpc - 1) / tpc), OTH_BLOCK, 0, q>>>(p, tpc);
+                }
+                if (!multi) k_step_fast<S, SRC><<<(unsigned)ntiles, OTH_BLOCK, 0, q>>>(p);
             }
         }
         if (!fast) k_step<S, SRC><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);

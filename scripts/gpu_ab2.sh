@@ -17,13 +17,10 @@ try:
 except Exception as e: print(sys.argv[2], "FAILED", e)
 PY
 }
-run head_main X=1 $H
 run head_tpc1 OTH_STEP_TPC=1 $H
 run head_tpc2 OTH_STEP_TPC=2 $H
+run head_tpc3 OTH_STEP_TPC=3 $H
 run head_tpc4 OTH_STEP_TPC=4 $H
-run head_c7 OTH_LIB_DIR=_lib_c7 $H
-run head_c8 OTH_LIB_DIR=_lib_c8 $H
-run head_c8_tpc1 OTH_LIB_DIR=_lib_c8 OTH_STEP_TPC=1 $H
-run sizes_main X=1 $Z
+run head_tpc8 OTH_STEP_TPC=8 $H
 run sizes_tpc1 OTH_STEP_TPC=1 $Z
-run sizes_rayold OTH_LIB_DIR=_lib_rayold $Z
+run sizes_tpc2 OTH_STEP_TPC=2 $Z

@@ -93,6 +93,7 @@ def test_clipped_ppo_surrogate_equals_the_per_env_loop():
     actions[2, 5, 0] = 0                                    # (0,0) is never legal on move 3: a "not in choices" row
     g = torch.Generator(device="cpu").manual_seed(3)
     idx = torch.randperm(T * Bn, generator=g)[:256]
+    idx[0] = 2 * Bn + 5                                     # the 'action not in choices' sample is in the minibatch
     lists = store.as_lists(idx)
     for j, i in enumerate(idx.tolist()):                    # gather order = storage.py's flattening (t * B + b)
         t, b = divmod(i, Bn)
