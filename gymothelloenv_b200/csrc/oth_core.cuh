@@ -382,7 +382,7 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
 
 // ---- multi-word boards: flips by carry propagation -------------------------------------
 #ifndef OTH_RAY_PROGRESSION
-#define OTH_RAY_PROGRESSION 1   // 0: round-1 ray masks (variable whole-board shift of a per-direction pattern), for A/B
+#define OTH_RAY_PROGRESSION 0   // 1: progression ray masks; measured 1-3 % SLOWER than the variable shift (profiles/r03e_experiments.md)
 #endif
 // whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
 template <int W> OTH_DEV BB<W> bb_shl_var(const BB<W> &x, int a) {

@@ -8,10 +8,12 @@
 // 512 contiguous bytes (st.global.v4), instead of 32 strided 64-byte rows.
 #pragma once
 #include <cuda_runtime.h>
-#include <cstdlib>
 #include "oth_core.cuh"
 #include "oth_coop_search.cuh"
 
+#ifndef OTH_NIB_SLAB
+#define OTH_NIB_SLAB 1     // 0: the register shift + mask slab writer on the fast path (A/B)
+#endif
 constexpr int OTH_BLOCK = 128;
 constexpr int OTH_WARPS = OTH_BLOCK / 32;
 
@@ -830,6 +832,53 @@ OTH_DEV void fast8_full_eo(void *base, i64 env0, const uint4 *pos_rows, const ui
     }
 }
 
+// Slab expansion through a per-lane NIBBLE stage (even sizes other than 8, fast path).  slab_expand pays, per 4
+// cells, a shift + mask to pull the nibble out of a register (3 ALU-pipe instructions per source word); here the
+// lane parks each 64-bit plane word as 16 nibbles-in-bytes (nibble_bytes_eo: 6 ALU-pipe instructions per 64 cells) in
+// its own row of shared memory and fetches every nibble back with one LDS.U8 at a compile-time offset -- the
+// extraction moves to the LSU pipe, as in the 8x8 writer.  Rows are 4W+1 words apart (odd): conflict-free.
+template <int S>
+struct NibStage {
+    static constexpr int W = Geo<S>::W, N = Geo<S>::N;
+    static constexpr int LANE_WORDS = 4 * W + 1;
+    static constexpr int PLANE_BYTES = 32 * LANE_WORDS * 4;
+    static constexpr int SLAB_OFFSET = 2 * PLANE_BYTES;                       // two planes (pos, neg), then the slab
+    static constexpr bool fits = SLAB_OFFSET + 32 * N <= (int)sizeof(WarpStage<S>) && SLAB_OFFSET % 16 == 0;
+};
+// byte offset of nibble q (cells 4q..4q+3 of one 64-bit word) inside its 16-byte nibble_bytes_eo group
+__host__ __device__ constexpr int nib_eo_offset(int q) { return ((q >> 3) * 2 + (q & 1)) * 4 + ((q & 7) >> 1); }
+template <int S, bool HAS_NEG>
+OTH_DEV void slab_expand_nib(unsigned char *stage_base, int lane, const BB<Geo<S>::W> &pos, const BB<Geo<S>::W> &neg) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W, G4 = N / 4;
+    using NS = NibStage<S>;
+    u32 *mine = reinterpret_cast<u32 *>(stage_base) + lane * NS::LANE_WORDS;
+    BB_FOR(k) {
+        const uint4 n = nibble_bytes_eo(pos.w[k]);
+        mine[4 * k] = n.x; mine[4 * k + 1] = n.y; mine[4 * k + 2] = n.z; mine[4 * k + 3] = n.w;
+        if constexpr (HAS_NEG) {
+            const uint4 m = nibble_bytes_eo(neg.w[k]);
+            u32 *mn = mine + NS::PLANE_BYTES / 4;
+            mn[4 * k] = m.x; mn[4 * k + 1] = m.y; mn[4 * k + 2] = m.z; mn[4 * k + 3] = m.w;
+        }
+    }
+    const u32 src = (u32)__cvta_generic_to_shared(mine);
+    u32 *dst = reinterpret_cast<u32 *>(stage_base + NS::SLAB_OFFSET + lane * N);
+    constexpr bool VEC = (N % 16 == 0) && ((N / 16) % 2 == 1);
+    u32 quad[4];
+#pragma unroll
+    for (int r = 0; r < G4; r++) {
+        const int off = (r >> 4) * 16 + nib_eo_offset(r & 15);
+        u32 w = spread4(lds_u8(src + off));
+        if constexpr (HAS_NEG) w = spread4(lds_u8(src + NS::PLANE_BYTES + off)) * 0xFFu + w;
+        if constexpr (VEC) {
+            quad[r & 3] = w;
+            if ((r & 3) == 3) reinterpret_cast<uint4 *>(dst)[r >> 2] = make_uint4(quad[0], quad[1], quad[2], quad[3]);
+        } else {
+            dst[r] = w;
+        }
+    }
+}
+
 // The headline output set with everything decided at compile time (oth_step dispatches here when it applies):
 // int8 `board` observation + dense legal mask, full warps only; S == 8 uses the even/odd nibble stage, the other
 // even sizes the slab writer.
@@ -853,24 +902,30 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
         __syncwarp();
     } else {
         static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
-        unsigned char *slab = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
-        slab_expand<S, true>(slab, lane, pos, neg);
-        __syncwarp();
-        slab_copy<S>(slab, out.obs, warp_env0, lane);
-        __syncwarp();
-        slab_expand<S, false>(slab, lane, lg, lg);
-        __syncwarp();
-        slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
-        __syncwarp();
+        unsigned char *base = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
+        if constexpr (OTH_NIB_SLAB && NibStage<S>::fits) {
+            unsigned char *slab = base + NibStage<S>::SLAB_OFFSET;
+            slab_expand_nib<S, true>(base, lane, pos, neg);
+            __syncwarp();
+            slab_copy<S>(slab, out.obs, warp_env0, lane);
+            __syncwarp();
+            slab_expand_nib<S, false>(base, lane, lg, lg);
+            __syncwarp();
+            slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
+            __syncwarp();
+        } else {
+            slab_expand<S, true>(base, lane, pos, neg);
+            __syncwarp();
+            slab_copy<S>(base, out.obs, warp_env0, lane);
+            __syncwarp();
+            slab_expand<S, false>(base, lane, lg, lg);
+            __syncwarp();
+            slab_copy<S>(base, out.legal_mask, warp_env0, lane);
+            __syncwarp();
+        }
     }
 }
 
-#ifndef OTH_STEP_TILES_PER_CTA
-#define OTH_STEP_TILES_PER_CTA 1   // default schedule of the fast step path (see SizeLaunch::fast_tiles_per_cta)
-#endif
-#ifndef OTH_STEP8_MULTI_MIN_CTAS
-#define OTH_STEP8_MULTI_MIN_CTAS 7   // the multi-tile 8x8 kernel is compiled for 7 resident CTAs per SM (72 registers)
-#endif
 #ifndef OTH_STEP8_MIN_CTAS
 #define OTH_STEP8_MIN_CTAS 0    // min resident CTAs per SM the 8x8 fast kernel is compiled for (0: compiler default; 8: register cap 64)
 #endif
@@ -923,7 +978,9 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
 
 // Fast kernels: B is a multiple of the CTA size, the scalars go to out.packed only and the dense outputs are the int8
 // `board` observation + legal mask (even S) -- no per-output null checks, no ragged-warp handling, no layout dispatch.
-// k_step_fast: one 128-env tile per CTA (the hardware's CTA scheduler staggers the CTAs' load / rules / store phases).
+// One 128-env tile per CTA: the hardware's CTA scheduler staggers the CTAs' load / rules / store phases.  Multi-tile
+// CTAs that prefetch the next tile's state (in registers, or staged in shared memory with cp.async) were built and
+// measured: 39.7-43.8 us against 38.9 us, slower the more tiles a CTA owns (profiles/r03e_experiments.md).
 template <int S, int SRC>
 __global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_step_fast(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
@@ -933,70 +990,6 @@ __global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_
     bool zero_obs = false;
     step_one_env<S, SRC, true>(p, e, i, SRC == OTH_ACT_EXTERNAL ? p.actions[i] : (i64)-1, zero_obs);
     emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
-}
-
-// k_step_fast_multi: a CTA steps `tiles_per_cta` tiles (tile t = blockIdx.x + j * gridDim.x).  With one tile per CTA
-// every warp sits out a DRAM round trip before its first instruction (`long_scoreboard` is the top stall, issue
-// slots ~30 % idle, profiles/r03a).  Here each thread copies the NEXT tile's state of "its" env into shared memory
-// with cp.async while it computes the current tile -- no registers are held across the tile (a register prefetch
-// cost 7 registers = one resident CTA per SM and lost more than it won, profiles/r03d) and, a thread reading back
-// only what it copied itself, no barrier is needed beyond cp.async.wait_group.  Two slots: the copy for tile j+1
-// must not land in the slot tile j is still read from.
-template <int S, bool WITH_ACTIONS>
-struct StateStage {
-    u64 bw[2][3 * Geo<S>::W][OTH_BLOCK];      // [slot][black words, white words, legal words][thread]
-    u32 mc[2][2][OTH_BLOCK];                  // [slot][meta, ctr][thread]
-    i64 act[2][WITH_ACTIONS ? OTH_BLOCK : 1];
-};
-OTH_DEV void cp_async8(void *smem, const void *gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-OTH_DEV void cp_async4(void *smem, const void *gmem) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((u32)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-template <int S, int SRC>
-OTH_DEV void stage_state_async(StateStage<S, SRC == OTH_ACT_EXTERNAL> &sb, int slot, const StepParams &p, i64 i) {
-    constexpr int W = Geo<S>::W;
-    const int tid = threadIdx.x;
-    BB_FOR(k) {
-        cp_async8(&sb.bw[slot][k][tid], &p.st.black[k * p.B + i]);
-        cp_async8(&sb.bw[slot][W + k][tid], &p.st.white[k * p.B + i]);
-        cp_async8(&sb.bw[slot][2 * W + k][tid], &p.st.legal[k * p.B + i]);
-    }
-    cp_async4(&sb.mc[slot][0][tid], &p.st.meta[i]);
-    cp_async4(&sb.mc[slot][1][tid], &p.st.ctr[i]);
-    if (SRC == OTH_ACT_EXTERNAL) cp_async8(&sb.act[slot][tid], &p.actions[i]);
-}
-template <int S, int SRC>
-__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MULTI_MIN_CTAS : 0) k_step_fast_multi(StepParams p, int tiles_per_cta) {
-    constexpr int W = Geo<S>::W;
-    __shared__ WarpStage<S> stage[OTH_WARPS];
-    __shared__ StateStage<S, SRC == OTH_ACT_EXTERNAL> sb;
-    const i64 ntiles = p.B / OTH_BLOCK;
-    const int tid = threadIdx.x;
-    i64 t = blockIdx.x;
-    if (t < ntiles) stage_state_async<S, SRC>(sb, 0, p, t * OTH_BLOCK + tid);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    for (int j = 0; j < tiles_per_cta && t < ntiles; j++, t += gridDim.x) {
-        const int slot = j & 1;
-        const i64 tn = t + gridDim.x;
-        if (j + 1 < tiles_per_cta && tn < ntiles) stage_state_async<S, SRC>(sb, slot ^ 1, p, tn * OTH_BLOCK + tid);
-        asm volatile("cp.async.commit_group;" ::: "memory");          // possibly empty: keeps the group count uniform
-        asm volatile("cp.async.wait_group 1;" ::: "memory");          // everything but the newest group: this tile is in
-        const i64 i = t * OTH_BLOCK + tid;
-        EnvRegs<S> e;
-        BB_FOR(k) {
-            e.black.w[k] = sb.bw[slot][k][tid];
-            e.white.w[k] = sb.bw[slot][W + k][tid];
-            e.legal.w[k] = sb.bw[slot][2 * W + k][tid];
-        }
-        e.meta = sb.mc[slot][0][tid];
-        e.ctr = sb.mc[slot][1][tid];
-        const i64 act = SRC == OTH_ACT_EXTERNAL ? sb.act[slot][tid] : (i64)-1;
-        bool zero_obs = false;
-        step_one_env<S, SRC, true>(p, e, i, act, zero_obs);
-        emit_board_mask_fast<S>(e, zero_obs, p.out, i - (threadIdx.x & 31), stage[threadIdx.x >> 5]);
-    }
 }
 
 // ------------------------------------------------------------------------- self-play
@@ -1580,17 +1573,6 @@ struct SizeLaunch {
         k_observe<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, flags, out);
         return cudaGetLastError();
     }
-    // tiles per CTA of the fast path: OTH_STEP_TPC (development A/B) or the measured default below.
-    // 1 = k_step_fast (one tile per CTA), n > 1 = k_step_fast_multi with n tiles per CTA and cp.async staging.
-    static int fast_tiles_per_cta() {
-        static int tpc = 0;                          // idempotent: racing threads compute the same value
-        if (tpc == 0) {
-            const char *v = getenv("OTH_STEP_TPC");
-            const int n = v ? atoi(v) : 0;
-            tpc = n > 0 ? n : OTH_STEP_TILES_PER_CTA;
-        }
-        return tpc;
-    }
     template <int SRC>
     static void step_src(const StepParams &p, cudaStream_t q) {
         const oth_outputs &o = p.out;
@@ -1599,16 +1581,7 @@ struct SizeLaunch {
             fast = p.B % OTH_BLOCK == 0 && o.packed != nullptr && o.obs != nullptr && o.legal_mask != nullptr &&
                    o.obs_layout == OTH_OBS_BOARD && o.obs_dtype == OTH_DTYPE_I8 && !o.reward && !o.done &&
                    !o.player_turn && !o.winner && !o.actions_out;
-            if (fast) {
-                const i64 ntiles = p.B / OTH_BLOCK;
-                const int tpc = fast_tiles_per_cta();
-                bool multi = false;
-                if constexpr (Geo<S>::W == 1) {          // the staged state of multi-word boards does not fit 48 KB
-                    multi = tpc > 1 && ntiles >= 4 * tpc;
-                    if (multi) k_step_fast_multi<S, SRC><<<(unsigned)((ntiles + tpc - 1) / tpc), OTH_BLOCK, 0, q>>>(p, tpc);
-                }
-                if (!multi) k_step_fast<S, SRC><<<(unsigned)ntiles, OTH_BLOCK, 0, q>>>(p);
-            }
+            if (fast) k_step_fast<S, SRC><<<(unsigned)(p.B / OTH_BLOCK), OTH_BLOCK, 0, q>>>(p);
         }
         if (!fast) k_step<S, SRC><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
     }

@@ -2,7 +2,7 @@
 # A/B of step-kernel schedules and variants.  usage (under gpurun): bash scripts/gpu_ab2.sh <tag>
 set -u
 TAG=$1; OUT=gpurun_out/$TAG; mkdir -p $OUT
-echo "== pytest -m gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 $OUT/pytest_gpu.log
+echo "== pytest -m gpu"; timeout 1500 python -m pytest ${PYTEST_ARGS:-tests} -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 $OUT/pytest_gpu.log
 H="python bench.py --steps 2000 --warmup 100 --no-cpu-baseline --e2e-steps 3"
 Z="python bench.py --config sizes --steps 300 --warmup 20 --no-cpu-baseline --e2e-steps 3"
 run() {  # name, env assignments..., -- command
@@ -17,10 +17,6 @@ try:
 except Exception as e: print(sys.argv[2], "FAILED", e)
 PY
 }
-run head_tpc1 OTH_STEP_TPC=1 $H
-run head_tpc2 OTH_STEP_TPC=2 $H
-run head_tpc3 OTH_STEP_TPC=3 $H
-run head_tpc4 OTH_STEP_TPC=4 $H
-run head_tpc8 OTH_STEP_TPC=8 $H
-run sizes_tpc1 OTH_STEP_TPC=1 $Z
-run sizes_tpc2 OTH_STEP_TPC=2 $Z
+run head_main X=1 $H
+run sizes_main X=1 $Z
+run sizes_nibslab0 OTH_LIB_DIR=_lib_nibslab0 $Z
