@@ -11,8 +11,8 @@
 #include "oth_core.cuh"
 #include "oth_coop_search.cuh"
 
-#ifndef OTH_NIB_SLAB
-#define OTH_NIB_SLAB 1     // 0: the register shift + mask slab writer on the fast path (A/B)
+#ifndef OTH_STEPN_MIN_CTAS
+#define OTH_STEPN_MIN_CTAS 0   // min resident CTAs per SM the fast step kernels of sizes other than 8 are compiled for
 #endif
 constexpr int OTH_BLOCK = 128;
 constexpr int OTH_WARPS = OTH_BLOCK / 32;
@@ -832,53 +832,6 @@ OTH_DEV void fast8_full_eo(void *base, i64 env0, const uint4 *pos_rows, const ui
     }
 }
 
-// Slab expansion through a per-lane NIBBLE stage (even sizes other than 8, fast path).  slab_expand pays, per 4
-// cells, a shift + mask to pull the nibble out of a register (3 ALU-pipe instructions per source word); here the
-// lane parks each 64-bit plane word as 16 nibbles-in-bytes (nibble_bytes_eo: 6 ALU-pipe instructions per 64 cells) in
-// its own row of shared memory and fetches every nibble back with one LDS.U8 at a compile-time offset -- the
-// extraction moves to the LSU pipe, as in the 8x8 writer.  Rows are 4W+1 words apart (odd): conflict-free.
-template <int S>
-struct NibStage {
-    static constexpr int W = Geo<S>::W, N = Geo<S>::N;
-    static constexpr int LANE_WORDS = 4 * W + 1;
-    static constexpr int PLANE_BYTES = 32 * LANE_WORDS * 4;
-    static constexpr int SLAB_OFFSET = 2 * PLANE_BYTES;                       // two planes (pos, neg), then the slab
-    static constexpr bool fits = SLAB_OFFSET + 32 * N <= (int)sizeof(WarpStage<S>) && SLAB_OFFSET % 16 == 0;
-};
-// byte offset of nibble q (cells 4q..4q+3 of one 64-bit word) inside its 16-byte nibble_bytes_eo group
-__host__ __device__ constexpr int nib_eo_offset(int q) { return ((q >> 3) * 2 + (q & 1)) * 4 + ((q & 7) >> 1); }
-template <int S, bool HAS_NEG>
-OTH_DEV void slab_expand_nib(unsigned char *stage_base, int lane, const BB<Geo<S>::W> &pos, const BB<Geo<S>::W> &neg) {
-    constexpr int N = Geo<S>::N, W = Geo<S>::W, G4 = N / 4;
-    using NS = NibStage<S>;
-    u32 *mine = reinterpret_cast<u32 *>(stage_base) + lane * NS::LANE_WORDS;
-    BB_FOR(k) {
-        const uint4 n = nibble_bytes_eo(pos.w[k]);
-        mine[4 * k] = n.x; mine[4 * k + 1] = n.y; mine[4 * k + 2] = n.z; mine[4 * k + 3] = n.w;
-        if constexpr (HAS_NEG) {
-            const uint4 m = nibble_bytes_eo(neg.w[k]);
-            u32 *mn = mine + NS::PLANE_BYTES / 4;
-            mn[4 * k] = m.x; mn[4 * k + 1] = m.y; mn[4 * k + 2] = m.z; mn[4 * k + 3] = m.w;
-        }
-    }
-    const u32 src = (u32)__cvta_generic_to_shared(mine);
-    u32 *dst = reinterpret_cast<u32 *>(stage_base + NS::SLAB_OFFSET + lane * N);
-    constexpr bool VEC = (N % 16 == 0) && ((N / 16) % 2 == 1);
-    u32 quad[4];
-#pragma unroll
-    for (int r = 0; r < G4; r++) {
-        const int off = (r >> 4) * 16 + nib_eo_offset(r & 15);
-        u32 w = spread4(lds_u8(src + off));
-        if constexpr (HAS_NEG) w = spread4(lds_u8(src + NS::PLANE_BYTES + off)) * 0xFFu + w;
-        if constexpr (VEC) {
-            quad[r & 3] = w;
-            if ((r & 3) == 3) reinterpret_cast<uint4 *>(dst)[r >> 2] = make_uint4(quad[0], quad[1], quad[2], quad[3]);
-        } else {
-            dst[r] = w;
-        }
-    }
-}
-
 // The headline output set with everything decided at compile time (oth_step dispatches here when it applies):
 // int8 `board` observation + dense legal mask, full warps only; S == 8 uses the even/odd nibble stage, the other
 // even sizes the slab writer.
@@ -903,17 +856,9 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
     } else {
         static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
         unsigned char *base = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
-        if constexpr (OTH_NIB_SLAB && NibStage<S>::fits) {
-            unsigned char *slab = base + NibStage<S>::SLAB_OFFSET;
-            slab_expand_nib<S, true>(base, lane, pos, neg);
-            __syncwarp();
-            slab_copy<S>(slab, out.obs, warp_env0, lane);
-            __syncwarp();
-            slab_expand_nib<S, false>(base, lane, lg, lg);
-            __syncwarp();
-            slab_copy<S>(slab, out.legal_mask, warp_env0, lane);
-            __syncwarp();
-        } else {
+        {
+            // (a nibble-staged expansion with LDS.U8 extraction, as in the 8x8 writer, measured 1-4 % slower here:
+            // profiles/r03e_experiments.md)
             slab_expand<S, true>(base, lane, pos, neg);
             __syncwarp();
             slab_copy<S>(base, out.obs, warp_env0, lane);
@@ -929,9 +874,6 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
 #ifndef OTH_STEP8_MIN_CTAS
 #define OTH_STEP8_MIN_CTAS 0    // min resident CTAs per SM the 8x8 fast kernel is compiled for (0: compiler default; 8: register cap 64)
 #endif
-// SRC: OTH_ACT_* at compile time.  FAST: B is a multiple of the CTA size, the scalars go to out.packed only, and
-// the dense outputs are the int8 `board` observation + legal mask (even S) -- no per-output null checks, no
-// ragged-warp handling, no layout dispatch.  Everything else runs the general instantiation.
 // One env's step (policy / opening override -> rules -> auto-reset -> state store -> scalars): shared by the
 // one-tile general kernel and the multi-tile fast kernel.  `ext_action` = the caller's action for OTH_ACT_EXTERNAL.
 template <int S, int SRC, bool PACKED_ONLY>
@@ -982,7 +924,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
 // CTAs that prefetch the next tile's state (in registers, or staged in shared memory with cp.async) were built and
 // measured: 39.7-43.8 us against 38.9 us, slower the more tiles a CTA owns (profiles/r03e_experiments.md).
 template <int S, int SRC>
-__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : 0) k_step_fast(StepParams p) {
+__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : OTH_STEPN_MIN_CTAS) k_step_fast(StepParams p) {
     __shared__ WarpStage<S> stage[OTH_WARPS];
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
     EnvRegs<S> e;
