@@ -38,8 +38,9 @@ OBS_NONE, OBS_BOARD, OBS_BOARD_MASK, OBS_PLANES4, OBS_PLANES3, OBS_ABSOLUTE = 0,
 OBS_PLANES = {OBS_NONE: 0, OBS_BOARD: 1, OBS_BOARD_MASK: 2, OBS_PLANES4: 4, OBS_PLANES3: 3, OBS_ABSOLUTE: 1}
 DTYPE_I8, DTYPE_F32 = 0, 1
 ACT_EXTERNAL, ACT_RANDOM, ACT_GREEDY = 0, 1, 2
-POLICY_RANDOM, POLICY_GREEDY, POLICY_MAXIMIN = 0, 1, 2
-MAX_SEARCH_DEPTH = 4
+POLICY_RANDOM, POLICY_GREEDY, POLICY_MAXIMIN, POLICY_ALPHABETA = 0, 1, 2, 3
+MAX_SEARCH_DEPTH = 8
+SEARCH_PRUNE, SEARCH_COOPERATIVE = 1, 2
 
 META_TURN_WHITE = 0x1
 META_TERMINATED = 0x2
@@ -52,7 +53,7 @@ EXPORTED_SYMBOLS = (
     "oth_policy", "oth_rollout", "oth_set_board", "oth_update_board", "oth_int_alu_probe",
     "oth_selfplay_new_game", "oth_selfplay_begin", "oth_selfplay_advance", "oth_masked_categorical",
     "oth_epsilon_greedy", "oth_ts_new_game", "oth_ts_begin", "oth_ts_advance", "oth_rollout_noalloc",
-    "oth_masked_logprob_forward", "oth_masked_logprob_backward",
+    "oth_masked_logprob_forward", "oth_masked_logprob_backward", "oth_search",
 )
 NOALLOC_MAX_GAMES = 1 << 21
 
@@ -127,6 +128,8 @@ def load():
     L.oth_policy.restype = C.c_int
     L.oth_policy.argtypes = [OthState, C.c_int64, C.c_int, OthPolicySpec, C.c_uint64, C.c_uint64, C.c_int64,
                              C.c_void_p, C.c_void_p]
+    L.oth_search.restype = C.c_int
+    L.oth_search.argtypes = [OthState, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     L.oth_rollout.restype = C.c_int
     L.oth_rollout.argtypes = [C.c_int64, C.c_int, C.c_int, OthPolicySpec, OthPolicySpec, C.c_int, C.c_int,
                               C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

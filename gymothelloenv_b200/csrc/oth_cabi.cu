@@ -109,10 +109,22 @@ OTH_API int oth_step(oth_state st, int64_t B, int board_size, int flags, int act
 }
 
 static int check_spec(const oth_policy_spec &s) {
-    if (s.kind < OTH_POLICY_RANDOM || s.kind > OTH_POLICY_MAXIMIN) return fail(OTH_ERR_BAD_ARG, "bad policy kind");
-    if (s.kind == OTH_POLICY_MAXIMIN && (s.depth < 1 || s.depth > OTH_MAX_SEARCH_DEPTH))
-        return fail(OTH_ERR_BAD_ARG, "maximin depth must be in 1..4");
+    if (s.kind < OTH_POLICY_RANDOM || s.kind > OTH_POLICY_ALPHABETA) return fail(OTH_ERR_BAD_ARG, "bad policy kind");
+    if (s.kind >= OTH_POLICY_MAXIMIN && (s.depth < 1 || s.depth > OTH_MAX_SEARCH_DEPTH))
+        return fail(OTH_ERR_BAD_ARG, "search depth must be in 1..8");
     return 0;
+}
+
+OTH_API int oth_search(oth_state st, int64_t B, int board_size, int depth, int flags, int64_t *actions_out,
+                       int64_t *nodes_out, void *stream) {
+    const OthSizeOps *ops;
+    if (int rc = check_state(st, B, board_size, &ops)) return rc;
+    if (depth < 1 || depth > OTH_MAX_SEARCH_DEPTH) return fail(OTH_ERR_BAD_ARG, "search depth must be in 1..8");
+    if (flags & ~(OTH_SEARCH_PRUNE | OTH_SEARCH_COOPERATIVE)) return fail(OTH_ERR_BAD_ARG, "bad search flags");
+    if (actions_out == nullptr) return fail(OTH_ERR_NULL_POINTER, "actions_out is null");
+    if (B == 0) return 0;
+    return cuda_result(ops->search(st, B, depth, (flags & OTH_SEARCH_PRUNE) ? 1 : 0, (flags & OTH_SEARCH_COOPERATIVE) ? 1 : 0,
+                                   (i64 *)actions_out, (i64 *)nodes_out, (cudaStream_t)stream), "oth_search");
 }
 
 OTH_API int oth_policy(oth_state st, int64_t B, int board_size, oth_policy_spec spec, uint64_t seed, uint64_t counter,

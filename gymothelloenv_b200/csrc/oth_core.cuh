@@ -813,12 +813,4 @@ struct MaxiMin {
     }
 };
 
-template <int S>
-__device__ int policy_pick(int kind, int depth, const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp,
-                           const BB<Geo<S>::W> &moves, u32 rnd) {
-    if (kind == OTH_POLICY_RANDOM) return random_pick<S>(moves, rnd);
-    if (kind == OTH_POLICY_GREEDY || depth <= 1) return greedy_pick<S>(own, opp, moves);   // README.md:54
-    if (depth == 2) return MaxiMin<S, 2>::pick(own, opp, moves);
-    if (depth == 3) return MaxiMin<S, 3>::pick(own, opp, moves);
-    return MaxiMin<S, 4>::pick(own, opp, moves);
-}
+// (policy_pick lives in oth_search.cuh: depths above 4 run the pruned generic-depth search)

@@ -9,6 +9,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "oth_core.cuh"
+#include "oth_search.cuh"
 #include "oth_coop_search.cuh"
 
 #ifndef OTH_STEPN_MIN_CTAS
@@ -1231,7 +1232,7 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_policy(oth_state s, i64 B, int ki
         u32 rnd = 0;
         if (kind == OTH_POLICY_RANDOM)
             rnd = philox_draw(seed, base + i, OTH_STREAM_POLICY + (u32)(counter >> 32), (u32)counter);
-        a = policy_pick<S>(kind, depth, bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal, rnd);
+        a = policy_pick<S, false>(kind, depth, bb_select(wm, e.white, e.black), bb_select(wm, e.black, e.white), e.legal, rnd);
     }
     actions_out[i] = a;
 }
@@ -1259,6 +1260,32 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_policy_coop(oth_state s, i64 B, i
     if (i < B) actions_out[i] = need ? a : -1;
 }
 
+// generic-depth maximin / alpha-beta (oth_search.cuh): per thread, or AB_GW lanes per position on single-word boards
+template <int S>
+__global__ void __launch_bounds__(OTH_BLOCK) k_search(oth_state s, i64 B, int depth, int prune, int cooperative,
+                                                      i64 *actions_out, i64 *nodes_out) {
+    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+    EnvRegs<S> e = empty_env<S>();
+    bool need = false;
+    if (i < B) {
+        load_env<S>(e, s, i, B);
+        need = !(e.meta & OTH_META_TERMINATED) && any(e.legal);
+    }
+    const bool wm = e.meta & OTH_META_TURN_WHITE;
+    const BB<Geo<S>::W> own = bb_select(wm, e.white, e.black), opp = bb_select(wm, e.black, e.white);
+    unsigned long long nodes = 0;
+    int a = -1;
+    if constexpr (Geo<S>::W == 1) {
+        if (cooperative) {                                       // warp-uniform: every lane takes part
+            a = coop_search_pick<S>(need, own.w[0], opp.w[0], e.legal.w[0], depth, prune != 0, nodes);
+            if (i < B) { actions_out[i] = need ? a : -1; if (nodes_out) nodes_out[i] = need ? (i64)nodes : 0; }
+            return;
+        }
+    }
+    if (need) a = search_pick<S>(own, opp, e.legal, depth, prune != 0, nodes);
+    if (i < B) { actions_out[i] = a; if (nodes_out) nodes_out[i] = (i64)nodes; }
+}
+
 // -------------------------------------------------------------------------- rollout
 struct RolloutParams {
     i64 B;
@@ -1279,7 +1306,7 @@ struct RolloutParams {
 
 // Whole games in registers, one thread per game, every decision per thread (random / greedy pairings, and
 // every multi-word board size).
-template <int S>
+template <int S, bool DEEP>
 __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
     const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
     u32 t_black = 0, t_draw = 0, t_white = 0, t_plies = 0;
@@ -1304,8 +1331,8 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout(RolloutParams p) {
                     e.ctr++;
                     if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
                 } else {
-                    a = policy_pick<S>(spec.kind, spec.depth, bb_select(wm, e.white, e.black),
-                                       bb_select(wm, e.black, e.white), e.legal, 0u);
+                    a = policy_pick<S, DEEP>(spec.kind, spec.depth, bb_select(wm, e.white, e.black),
+                                             bb_select(wm, e.black, e.white), e.legal, 0u);
                 }
                 if (p.trace != nullptr && ply < p.trace_stride) p.trace[game * p.trace_stride + ply] = (int16_t)a;
                 r = env_step<S>(e, a, p.flags);
@@ -1370,10 +1397,10 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_rollout_coop(RolloutParams p) {
                     a = random_pick<S>(e.legal, philox_draw_cached(rng, p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
                     e.ctr++;
                     if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
-                } else if (W == 1 && spec.kind == OTH_POLICY_MAXIMIN && spec.depth >= 2 && any(e.legal)) {
-                    coop_depth = min(spec.depth, 4);
+                } else if (W == 1 && spec.kind == OTH_POLICY_MAXIMIN && spec.depth >= 2 && spec.depth <= 4 && any(e.legal)) {
+                    coop_depth = spec.depth;
                 } else {
-                    a = policy_pick<S>(spec.kind, spec.depth, own, opp, e.legal, 0u);
+                    a = policy_pick<S, false>(spec.kind, spec.depth, own, opp, e.legal, 0u);
                 }
             }
             if constexpr (W == 1) {
@@ -1500,6 +1527,7 @@ struct OthSizeOps {
     cudaError_t (*selfplay_new_game)(oth_state, oth_selfplay, i64, u64, i64, int, u32, const int8_t *, cudaStream_t);
     cudaError_t (*teacher_student)(const TeacherStudentParams &, cudaStream_t);
     cudaError_t (*ts_new_game)(oth_state, oth_teacher_student, i64, u64, i64, int, cudaStream_t);
+    cudaError_t (*search)(oth_state, i64, int, int, int, i64 *, i64 *, cudaStream_t);
 };
 
 static inline unsigned oth_grid(i64 B) { return (unsigned)((B + OTH_BLOCK - 1) / OTH_BLOCK); }
@@ -1540,10 +1568,14 @@ struct SizeLaunch {
         if constexpr (Geo<S>::W == 1) {
             // measured on 2^18 mid-game 8x8 positions, cooperative vs per-thread DFS: depth 2 0.51 vs 0.73 ms,
             // depth 3 4.8 vs 12.6 ms, depth 4 60 vs 202 ms (profiles/r01p_policy.md)
-            if (kind == OTH_POLICY_MAXIMIN && depth >= 2) {
+            if (kind == OTH_POLICY_MAXIMIN && depth >= 2 && depth <= 4) {
                 k_policy_coop<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, depth, out);
                 return cudaGetLastError();
             }
+        }
+        if ((kind == OTH_POLICY_MAXIMIN && depth > 4) || kind == OTH_POLICY_ALPHABETA) {   // same choice, pruned search
+            k_search<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, depth, 1, Geo<S>::W == 1 ? 1 : 0, out, nullptr);
+            return cudaGetLastError();
         }
         k_policy<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, kind, depth, seed, counter, base, out);
         return cudaGetLastError();
@@ -1551,10 +1583,13 @@ struct SizeLaunch {
     static cudaError_t rollout(const RolloutParams &p0, cudaStream_t q) {
         RolloutParams p = p0;
         p.keys = philox_round_keys(p.seed);
-        const bool searches = (p.black.kind == OTH_POLICY_MAXIMIN && p.black.depth >= 2) ||
-                              (p.white.kind == OTH_POLICY_MAXIMIN && p.white.depth >= 2);
-        if (Geo<S>::W == 1 && searches && !(p.flags & OTH_F_SEARCH_PER_THREAD)) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
-        else k_rollout<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        const bool deep = (p.black.kind >= OTH_POLICY_MAXIMIN && p.black.depth > 4) || p.black.kind == OTH_POLICY_ALPHABETA ||
+                          (p.white.kind >= OTH_POLICY_MAXIMIN && p.white.depth > 4) || p.white.kind == OTH_POLICY_ALPHABETA;
+        const bool searches = !deep && ((p.black.kind == OTH_POLICY_MAXIMIN && p.black.depth >= 2) ||
+                                        (p.white.kind == OTH_POLICY_MAXIMIN && p.white.depth >= 2));
+        if (deep) k_rollout<S, true><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        else if (Geo<S>::W == 1 && searches && !(p.flags & OTH_F_SEARCH_PER_THREAD)) k_rollout_coop<S><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        else k_rollout<S, false><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
         return cudaGetLastError();
     }
     static cudaError_t set_board(oth_state s, i64 B, const int8_t *cells, const int8_t *persp, const int8_t *turn,
@@ -1584,9 +1619,14 @@ struct SizeLaunch {
         k_ts_new_game<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, ts, B, seed, base, init_rand);
         return cudaGetLastError();
     }
+    static cudaError_t search(oth_state s, i64 B, int depth, int prune, int cooperative, i64 *actions, i64 *nodes,
+                              cudaStream_t q) {
+        k_search<S><<<oth_grid(B), OTH_BLOCK, 0, q>>>(s, B, depth, prune, Geo<S>::W == 1 ? cooperative : 0, actions, nodes);
+        return cudaGetLastError();
+    }
     static const OthSizeOps *ops() {
         static const OthSizeOps o = {S, Geo<S>::W, &reset, &observe, &step, &policy, &rollout, &set_board, &update_board,
-                                     &selfplay, &selfplay_new_game, &teacher_student, &ts_new_game};
+                                     &selfplay, &selfplay_new_game, &teacher_student, &ts_new_game, &search};
         return &o;
     }
 };

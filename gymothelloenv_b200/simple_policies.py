@@ -99,7 +99,8 @@ class GreedyPolicy(_PolicyBase):
 
 
 class MaxiMinPolicy(_PolicyBase):
-    """Depth-k maximin on own disc count, no pruning (simple_policies.py:98-163).
+    """Depth-k maximin on own disc count (simple_policies.py:98-163).  Depths 1..4 search every node as the reference
+    does; depths 5..8 (the reference accepts any depth) run the alpha-beta search, which returns the same move.
     The `obs` argument is ignored, as in the reference (:157-163)."""
 
     def __init__(self, max_search_depth=1):
@@ -113,6 +114,18 @@ class MaxiMinPolicy(_PolicyBase):
         if env.terminated or not env.possible_moves:
             return None                                           # search() returns (count, None) at a leaf
         return _device_pick(env, "maximin", int(self.max_search_depth))
+
+
+class AlphaBetaPolicy(MaxiMinPolicy):
+    """MaxiMinPolicy with alpha-beta pruning (the reference's README.md:55-56: "can be improved by pruning (not
+    included)"): the SAME move as MaxiMinPolicy(depth) -- full window at the root, first-occurrence ties -- for a
+    fraction of the positions searched."""
+
+    def get_action(self, obs):
+        env = self._base_env()
+        if env.terminated or not env.possible_moves:
+            return None
+        return _device_pick(env, "alphabeta", int(self.max_search_depth))
 
 
 class HumanPolicy(object):

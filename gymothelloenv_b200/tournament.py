@@ -23,7 +23,7 @@ def parse_policy(spec):
     if isinstance(spec, (tuple, list)):
         return str(spec[0]), int(spec[1]) if len(spec) > 1 else 1
     s = str(spec)
-    for name in ("maximin", "rand", "random", "greedy"):
+    for name in ("maximin", "alphabeta", "rand", "random", "greedy"):
         if s.startswith(name):
             tail = s[len(name):].lstrip("-_")
             return name, int(tail) if tail else 1

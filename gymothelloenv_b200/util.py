@@ -9,7 +9,7 @@ empty when exactly one move exists (``util.py:55``).
 import numpy as np
 import torch
 
-from .simple_policies import GreedyPolicy, HumanPolicy, MaxiMinPolicy, RandomPolicy, undo_state  # noqa: F401
+from .simple_policies import AlphaBetaPolicy, GreedyPolicy, HumanPolicy, MaxiMinPolicy, RandomPolicy, undo_state  # noqa: F401
 
 
 def create_policy(policy_type='rand', board_size=8, seed=0, search_depth=1, agent_name='', device=None):
@@ -18,12 +18,14 @@ def create_policy(policy_type='rand', board_size=8, seed=0, search_depth=1, agen
         return RandomPolicy(seed=seed)
     if policy_type == 'greedy':
         return GreedyPolicy()
+    if policy_type == 'alphabeta':
+        return AlphaBetaPolicy(search_depth)
     if policy_type == 'maximin':
         return MaxiMinPolicy(search_depth)
     if policy_type == 'human':
         return HumanPolicy(board_size)
     raise ValueError("policy_type %r is not provided by gymothelloenv_b200 "
-                     "(rand | greedy | maximin | human)" % (policy_type,))
+                     "(rand | greedy | maximin | alphabeta | human)" % (policy_type,))
 
 
 def make_state(obs, env):

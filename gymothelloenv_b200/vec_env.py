@@ -27,7 +27,7 @@ _LAYOUTS = {
 }
 _DTYPES = {torch.int8: _cabi.DTYPE_I8, torch.float32: _cabi.DTYPE_F32}
 _POLICY_KINDS = {"rand": _cabi.POLICY_RANDOM, "random": _cabi.POLICY_RANDOM, "greedy": _cabi.POLICY_GREEDY,
-                 "maximin": _cabi.POLICY_MAXIMIN}
+                 "maximin": _cabi.POLICY_MAXIMIN, "alphabeta": _cabi.POLICY_ALPHABETA}
 _ACT_SOURCES = {"random": _cabi.ACT_RANDOM, "rand": _cabi.ACT_RANDOM, "greedy": _cabi.ACT_GREEDY}
 
 
@@ -44,10 +44,10 @@ _NULL_CTX = _NullCtx()
 
 def policy_spec(kind, depth=1):
     if kind not in _POLICY_KINDS:
-        raise ValueError("unknown policy kind %r (rand | greedy | maximin)" % (kind,))
+        raise ValueError("unknown policy kind %r (rand | greedy | maximin | alphabeta)" % (kind,))
     depth = int(depth)
-    if _POLICY_KINDS[kind] == _cabi.POLICY_MAXIMIN and not (1 <= depth <= _cabi.MAX_SEARCH_DEPTH):
-        raise ValueError("maximin search depth must be in 1..%d" % _cabi.MAX_SEARCH_DEPTH)
+    if _POLICY_KINDS[kind] >= _cabi.POLICY_MAXIMIN and not (1 <= depth <= _cabi.MAX_SEARCH_DEPTH):
+        raise ValueError("search depth must be in 1..%d" % _cabi.MAX_SEARCH_DEPTH)
     return _cabi.OthPolicySpec(_POLICY_KINDS[kind], max(1, depth))
 
 
@@ -437,3 +437,15 @@ class VecOthelloEnv(object):
                         "oth_policy")
         self._policy_counter += 1
         return out
+
+    def search_actions(self, depth, prune=True, cooperative=True, with_nodes=False):
+        """MaxiMinPolicy.get_action at any depth 1..8 for every env (oth_search): -> actions int64 [B], or
+        (actions, positions scored per env int64 [B]) with with_nodes.  prune: alpha-beta (same moves, fewer
+        positions); cooperative: 8 lanes per position on boards up to 8x8."""
+        flags = (_cabi.SEARCH_PRUNE if prune else 0) | (_cabi.SEARCH_COOPERATIVE if cooperative else 0)
+        out = torch.empty((self.num_envs,), dtype=torch.int64, device=self.device)
+        nodes = torch.zeros((self.num_envs,), dtype=torch.int64, device=self.device) if with_nodes else None
+        with self._on_device():
+            _cabi.check(self._lib.oth_search(self._state(), self.num_envs, self.board_size, int(depth), flags,
+                                             _cabi.ptr(out), _cabi.ptr(nodes), self._stream()), "oth_search")
+        return (out, nodes) if with_nodes else out

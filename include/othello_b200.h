@@ -92,7 +92,10 @@ typedef struct oth_state {
 #define OTH_POLICY_RANDOM  0
 #define OTH_POLICY_GREEDY  1
 #define OTH_POLICY_MAXIMIN 2
-#define OTH_MAX_SEARCH_DEPTH 4
+#define OTH_POLICY_ALPHABETA 3  /* maximin with alpha-beta pruning (README.md:55-56 "can be improved by pruning"): the
+                                   SAME move as OTH_POLICY_MAXIMIN at the same depth, fewer positions searched */
+#define OTH_MAX_SEARCH_DEPTH 8  /* MAXIMIN depth 2..4: full-width kernels (lane-cooperative on boards <= 8x8); depth
+                                   5..8 runs the pruned search -- same choice, never a silently shallower one */
 
 #define OTH_ERR_BAD_ARG        1001
 #define OTH_ERR_BAD_BOARD_SIZE 1002
@@ -119,7 +122,7 @@ typedef struct oth_outputs {
 
 typedef struct oth_policy_spec {
     int32_t kind;    /* OTH_POLICY_* */
-    int32_t depth;   /* maximin search depth 1..OTH_MAX_SEARCH_DEPTH (simple_policies.py:101-103) */
+    int32_t depth;   /* maximin / alpha-beta search depth 1..OTH_MAX_SEARCH_DEPTH (simple_policies.py:101-103) */
 } oth_policy_spec;
 
 int         oth_abi_version(void);
@@ -157,6 +160,16 @@ int oth_step(oth_state st, int64_t B, int board_size, int flags, int action_sour
  * own stream (callers pass their step index). */
 int oth_policy(oth_state st, int64_t B, int board_size, oth_policy_spec spec, uint64_t seed,
                uint64_t counter, int64_t env_id_base, int64_t *actions_out, void *stream);
+
+/* MaxiMinPolicy.get_action (simple_policies.py:111-163) at any depth 1..OTH_MAX_SEARCH_DEPTH for the side to move in
+ * every env, with the search's cost exposed: flags & OTH_SEARCH_PRUNE = alpha-beta pruning (same moves as without:
+ * full window at the root, first-occurrence argmax kept), flags & OTH_SEARCH_COOPERATIVE = 8 lanes per position
+ * (boards <= 8x8; the replies to the first root move, then the other root moves, are searched side by side).
+ * actions_out[i] = the move (-1 for finished envs / no move); nodes_out[i] (may be NULL) = positions scored. */
+#define OTH_SEARCH_PRUNE       0x1
+#define OTH_SEARCH_COOPERATIVE 0x2
+int oth_search(oth_state st, int64_t B, int board_size, int depth, int flags, int64_t *actions_out, int64_t *nodes_out,
+               void *stream);
 
 /* Fused tournament (run_2agent.py:92-203 with fixed colours; rule_base_game,
  * ppo_run_self_play.py:371-441): every env plays games_per_env complete games, black

@@ -11,6 +11,7 @@
 #define __device__
 #define __host__
 #define __forceinline__ inline
+#define __noinline__
 static inline unsigned long long __brevll(unsigned long long x) {
     unsigned long long r = 0;
     for (int i = 0; i < 64; i++) r |= ((x >> i) & 1ull) << (63 - i);
@@ -29,6 +30,7 @@ using std::max;
 using std::min;
 
 #include "../../gymothelloenv_b200/csrc/oth_core.cuh"
+#include "../../gymothelloenv_b200/csrc/oth_search.cuh"
 
 template <int S>
 static void step_batch(int64_t B, uint64_t *black, uint64_t *white, uint64_t *legal_, uint32_t *meta, const int64_t *actions,
@@ -65,7 +67,22 @@ static void policy_batch(int64_t B, const uint64_t *black, const uint64_t *white
         for (int k = 0; k < W; k++) { b.w[k] = black[k * B + i]; w.w[k] = white[k * B + i]; l.w[k] = legal_[k * B + i]; }
         if ((meta[i] & OTH_META_TERMINATED) || !any(l)) { out[i] = -1; continue; }
         const bool wm = meta[i] & OTH_META_TURN_WHITE;
-        out[i] = policy_pick<S>(kind, depth, wm ? w : b, wm ? b : w, l, 0u);
+        out[i] = policy_pick<S, true>(kind, depth, wm ? w : b, wm ? b : w, l, 0u);
+    }
+}
+// generic-depth maximin with / without alpha-beta pruning: action and positions scored per env
+template <int S>
+static void search_batch(int64_t B, const uint64_t *black, const uint64_t *white, const uint64_t *legal_, const uint32_t *meta,
+                         int depth, int prune, int64_t *out, int64_t *nodes_out) {
+    constexpr int W = Geo<S>::W;
+    for (int64_t i = 0; i < B; i++) {
+        BB<W> b, w, l;
+        for (int k = 0; k < W; k++) { b.w[k] = black[k * B + i]; w.w[k] = white[k * B + i]; l.w[k] = legal_[k * B + i]; }
+        unsigned long long nodes = 0;
+        if ((meta[i] & OTH_META_TERMINATED) || !any(l)) { out[i] = -1; nodes_out[i] = 0; continue; }
+        const bool wm = meta[i] & OTH_META_TURN_WHITE;
+        out[i] = search_pick<S>(wm ? w : b, wm ? b : w, l, depth, prune != 0, nodes);
+        nodes_out[i] = (int64_t)nodes;
     }
 }
 // n-th set bit of the cached legal set (the random policy's pick for a given index)
@@ -105,6 +122,13 @@ int emul_step(int S, int64_t B, uint64_t *black, uint64_t *white, uint64_t *lega
 int emul_policy(int S, int64_t B, const uint64_t *black, const uint64_t *white, const uint64_t *legal_, const uint32_t *meta,
                 int kind, int depth, int64_t *out) {
 #define CALL(N) policy_batch<N>(B, black, white, legal_, meta, kind, depth, out)
+    DISPATCH(S, CALL)
+#undef CALL
+    return 0;
+}
+int emul_search(int S, int64_t B, const uint64_t *black, const uint64_t *white, const uint64_t *legal_, const uint32_t *meta,
+                int depth, int prune, int64_t *out, int64_t *nodes_out) {
+#define CALL(N) search_batch<N>(B, black, white, legal_, meta, depth, prune, out, nodes_out)
     DISPATCH(S, CALL)
 #undef CALL
     return 0;

@@ -150,11 +150,11 @@ def test_output_descriptor_checks(lib):
 
 def test_policy_spec_checks(lib):
     st = _state()
-    assert lib.oth_policy(st, 8, 8, _spec(kind=3), 0, 0, 0, FAKE, None) == ERR_BAD_ARG
+    assert lib.oth_policy(st, 8, 8, _spec(kind=4), 0, 0, 0, FAKE, None) == ERR_BAD_ARG
     assert _err(lib) == "bad policy kind"
     for depth in (0, -2, _cabi.MAX_SEARCH_DEPTH + 1):
         assert lib.oth_policy(st, 8, 8, _spec(_cabi.POLICY_MAXIMIN, depth), 0, 0, 0, FAKE, None) == ERR_BAD_ARG
-        assert _err(lib) == "maximin depth must be in 1..4"
+        assert _err(lib) == "search depth must be in 1..8"
         assert lib.oth_rollout(8, 8, 0, _spec(), _spec(_cabi.POLICY_MAXIMIN, depth), 0, 1, 0, 0, FAKE, None, None, None,
                                None, 0, None) == ERR_BAD_ARG
     assert lib.oth_policy(st, 8, 8, _spec(), 0, 0, 0, None, None) == ERR_NULL_POINTER
@@ -162,6 +162,21 @@ def test_policy_spec_checks(lib):
     assert lib.oth_rollout(8, 8, 0, _spec(), _spec(), 0, 1, 0, 0, FAKE, None, None, None, FAKE, 0, None) == ERR_BAD_ARG
     assert _err(lib) == "trace_stride must be positive"
     assert lib.oth_update_board(st, 8, 8, None, None) == ERR_NULL_POINTER
+    # oth_search: depth range, flags, null output
+    for depth in (0, _cabi.MAX_SEARCH_DEPTH + 1):
+        assert lib.oth_search(st, 8, 8, depth, 0, FAKE, None, None) == ERR_BAD_ARG
+        assert _err(lib) == "search depth must be in 1..8"
+    assert lib.oth_search(st, 8, 8, 3, 4, FAKE, None, None) == ERR_BAD_ARG
+    assert _err(lib) == "bad search flags"
+    assert lib.oth_search(st, 8, 8, 3, _cabi.SEARCH_PRUNE, None, None, None) == ERR_NULL_POINTER
+    assert lib.oth_search(st, 0, 8, 3, _cabi.SEARCH_PRUNE, FAKE, None, None) == 0
+    # the differentiable evaluate_actions pair
+    assert lib.oth_masked_logprob_forward(None, FAKE, 8, 8, FAKE, FAKE, FAKE, None) == ERR_NULL_POINTER
+    assert lib.oth_masked_logprob_forward(FAKE, FAKE, 8, 8, FAKE, None, None, None) == ERR_NULL_POINTER
+    assert _err(lib) == "no output requested"
+    assert lib.oth_masked_logprob_backward(FAKE, FAKE, 8, 8, FAKE, FAKE, FAKE, None, None) == ERR_NULL_POINTER
+    assert _err(lib) == "grad_logits is null"
+    assert lib.oth_masked_logprob_backward(FAKE, FAKE, 0, 8, FAKE, FAKE, FAKE, FAKE, None) == 0
 
 
 def test_sampler_argument_checks(lib):
@@ -200,7 +215,7 @@ def test_selfplay_and_teacher_student_argument_checks(lib):
 def test_last_error_is_thread_local(lib):
     """SURVEY 8(b) Threading: no global mutable state -- a failure on one host thread does not overwrite the message
     another thread reads."""
-    assert lib.oth_policy(_state(), 8, 8, _spec(kind=3), 0, 0, 0, FAKE, None) == ERR_BAD_ARG
+    assert lib.oth_policy(_state(), 8, 8, _spec(kind=4), 0, 0, 0, FAKE, None) == ERR_BAD_ARG
     seen = {}
 
     def other():

@@ -17,6 +17,7 @@ from oracle import oracle
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "host_emul", "emul_core.cpp")
 CORE = os.path.join(os.path.dirname(HERE), "gymothelloenv_b200", "csrc", "oth_core.cuh")
+SEARCH = os.path.join(os.path.dirname(HERE), "gymothelloenv_b200", "csrc", "oth_search.cuh")
 LIB = os.path.join(os.path.dirname(HERE), "oracle", "_build", "libcore_host_emul.so")
 
 F_SUDDEN, F_DISK = 1, 2
@@ -28,7 +29,7 @@ def _p(a):
 
 @pytest.fixture(scope="module")
 def emul():
-    newest = max(os.path.getmtime(SRC), os.path.getmtime(CORE))
+    newest = max(os.path.getmtime(SRC), os.path.getmtime(CORE), os.path.getmtime(SEARCH))
     if not (os.path.isfile(LIB) and os.path.getmtime(LIB) >= newest):
         os.makedirs(os.path.dirname(LIB), exist_ok=True)
         tmp = LIB + ".%d.tmp" % os.getpid()
@@ -61,6 +62,13 @@ class EmulVec(object):
         assert self.lib.emul_policy(self.S, C.c_int64(self.B), _p(self.black), _p(self.white), _p(self.legal),
                                     _p(self.meta), kind, depth, _p(out)) == 0
         return out
+
+    def search(self, depth, prune):
+        out = np.zeros(self.B, dtype=np.int64)
+        nodes = np.zeros(self.B, dtype=np.int64)
+        assert self.lib.emul_search(self.S, C.c_int64(self.B), _p(self.black), _p(self.white), _p(self.legal),
+                                    _p(self.meta), depth, int(prune), _p(out), _p(nodes)) == 0
+        return out, nodes
 
     def _bits(self, words):
         N = self.S * self.S
@@ -132,6 +140,40 @@ def test_policy_picks_match_oracle(emul, S, depths):
             acts[i] = moves[rng.randint(len(moves))] if len(moves) else 0
         orc.step(acts)
         ev.step(acts, F_SUDDEN)
+
+
+@pytest.mark.parametrize("S,depths", [(4, (1, 2, 3, 4, 5, 6, 7, 8)), (5, (1, 3, 5, 6)), (6, (1, 2, 3, 4, 5)), (8, (1, 2, 3, 4)),
+                                      (10, (1, 2, 3)), (13, (1, 2))])
+def test_alpha_beta_search_matches_oracle_maximin(emul, S, depths):
+    """search_pick (oth_search.cuh): the pruned and the unpruned generic-depth search choose the move the oracle's
+    plain maximin chooses (first-occurrence ties), at every depth; pruning never scores more positions."""
+    B = 12
+    rng = np.random.RandomState(11 * S)
+    ev, orc = EmulVec(emul, B, S), oracle.OracleVec(B, S)
+    checked = 0
+    for t in range(S * S):
+        board, legal, turn, term, _, _ = orc.export()
+        if term.all():
+            break
+        if t % 5 == 2:
+            live = term == 0
+            for d in depths:
+                want = orc.policy("maximin", d)
+                a0, n0 = ev.search(d, False)
+                a1, n1 = ev.search(d, True)
+                assert np.array_equal(a0[live], want[live]), (S, t, d, "unpruned")
+                assert np.array_equal(a1[live], want[live]), (S, t, d, "pruned")
+                assert (n1 <= n0).all() and (d > 2 or True)
+                if d == 1:
+                    assert np.array_equal(n0, n1)
+                checked += int(live.sum())
+        acts = np.zeros(B, dtype=np.int64)
+        for i in range(B):
+            moves = np.flatnonzero(legal[i])
+            acts[i] = moves[rng.randint(len(moves))] if len(moves) else 0
+        orc.step(acts)
+        ev.step(acts, F_SUDDEN)
+    assert checked > 20
 
 
 def test_nth_set_bit(emul):
