@@ -100,10 +100,14 @@ def test_policy_parsing_and_validation():
     assert parse_policy("rand") == ("rand", 1) and parse_policy("maximin3") == ("maximin", 3)
     assert parse_policy(("maximin", 2)) == ("maximin", 2) and parse_policy("maximin-2") == ("maximin", 2)
     assert parse_policy("greedy") == ("greedy", 1)
+    assert parse_policy("alphabeta5") == ("alphabeta", 5) and parse_policy("alphabeta") == ("alphabeta", 1)
     with pytest.raises(ValueError):
-        parse_policy("alphabeta")
+        parse_policy("mcts4")
     with pytest.raises(ValueError):
         policy_spec("maximin", 9)
+    with pytest.raises(ValueError):
+        policy_spec("alphabeta", 0)
+    assert (policy_spec("alphabeta", 6).kind, policy_spec("maximin", 8).depth) == (3, 8)
     with pytest.raises(ValueError):
         policy_spec("mcts")
     s = policy_spec("maximin", 3)
