@@ -185,3 +185,49 @@ def int_fraction(entry, units_per_s, peak_inst_per_s):
 
 def emit(line):
     print(json.dumps(line), flush=True)
+
+
+def bind_to_gpu_numa_node(torch, local_rank):
+    """Pinned host buffers are placed by first touch: run this process on the cores of the NUMA node its GPU hangs
+    off BEFORE allocating them (the e2e path is a PCIe + host-memory workload).  -> node id or None."""
+    try:
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = getattr(torch.cuda.get_device_properties(local_rank), "pci_domain_id", 0)
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.extend(range(int(a), int(b or a) + 1))
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return node
+    except Exception:
+        return None
+
+
+def host_copy_ceiling(torch, ranks, d2h_bytes, h2d_bytes, iters):
+    """What the box gives a step that ONLY moves the e2e path's bytes: every rank copies h2d_bytes in and d2h_bytes
+    out through pinned buffers `iters` times, all ranks at once (the 8 ranks of a node share one host memory system).
+    -> GB/s per GPU (max-over-ranks time)."""
+    dev = ranks.dev
+    d_out = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+    h_out = torch.empty(d2h_bytes, dtype=torch.uint8, pin_memory=True)
+    d_in = torch.empty(max(1, h2d_bytes), dtype=torch.uint8, device=dev)
+    h_in = torch.empty(max(1, h2d_bytes), dtype=torch.uint8, pin_memory=True)
+    for _ in range(2):
+        d_in.copy_(h_in, non_blocking=True)
+        h_out.copy_(d_out, non_blocking=True)
+    ranks.barrier()
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        d_in.copy_(h_in, non_blocking=True)
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+    ranks.barrier()
+    dt = ranks.max_over_ranks(time.perf_counter() - t0)
+    return (d2h_bytes + h2d_bytes) * iters / dt / 1e9

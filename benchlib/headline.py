@@ -67,6 +67,8 @@ def run(args):
     from gymothelloenv_b200 import VecOthelloEnv
     ranks = common.Ranks(torch)
     dev, rank, world = ranks.dev, ranks.rank, ranks.world
+    all_cpus = os.sched_getaffinity(0)
+    numa = common.bind_to_gpu_numa_node(torch, ranks.local)     # before any pinned allocation
     B, K, W = args.num_envs, args.steps, max(3, args.warmup)
 
     env = VecOthelloEnv(B, board_size=8, device=dev, seed=0, auto_reset=True, obs_layout="board",
@@ -123,9 +125,14 @@ def run(args):
     # ---- e2e through host buffers: dense (the headline e2e) and the packed variant beside it ----
     Ke = max(3, args.e2e_steps)
     e2e = e2e_host_buffers(torch, ranks, env, B, Ke)
-    e2e_packed = None
-    if hasattr(env, "step_host") and "packed" in env.step_host.__code__.co_varnames:
-        e2e_packed = e2e_host_buffers(torch, ranks, env, B, Ke, packed=True)
+    e2e_packed = e2e_host_buffers(torch, ranks, env, B, Ke, packed=True)
+    # the box's ceiling for a step that only moves those bytes (all ranks at once), and e2e as a fraction of it
+    for r in (e2e, e2e_packed):
+        ceil_gbs = common.host_copy_ceiling(torch, ranks, r["d2h_bytes_per_step"], r["h2d_bytes_per_step"], Ke)
+        r["host_copy_ceiling_gbs_per_gpu"] = ceil_gbs
+        r["frac_of_host_copy_ceiling"] = r["host_link_gbs_per_gpu"] / ceil_gbs
+    e2e["numa_node_of_rank0"] = numa
+    os.sched_setaffinity(0, all_cpus)                           # the CPU baseline below uses every core again
 
     # ---- CPU baseline (rank 0, N = 1 only) ----
     cpu = None
