@@ -127,3 +127,20 @@ def test_step_host_packed_expands_to_the_dense_outputs(S):
         assert np.array_equal(o2, obs[sub]) and np.array_equal(m2, mask[sub])
     h2d, d2h = pk.host_bytes_per_step()
     assert h2d == 2 * B and d2h == B * (24 * pk.words + 6)
+
+
+def test_the_stub_in_integration_md_runs_as_written():
+    """INTEGRATION.md section B is the binding a maintainer of the reference would copy: execute it verbatim."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    section = text[text.index("## B. The ctypes stub"):text.index("## C. Batched use")]
+    code = re.search(r"```python\n(.*?)```", section, flags=re.S).group(1)
+    code = code.replace('"gymothelloenv_b200/_lib/libothello_b200.so"', repr(_cabi.LIB_PATH))
+    scope = {}
+    exec(compile(code, "INTEGRATION.md:B", "exec"), scope)
+    torch.cuda.synchronize()
+    assert scope["mask"][0].nonzero().flatten().tolist() == [18, 20, 34]              # white's replies to 19 (oracle)
+    assert float(scope["reward"][0]) == 0.0 and not bool(scope["done"][0]) and int(scope["turn"][0]) == 1
+    assert int(scope["obs"][0].sum()) == -3                                          # mover white: 1 own, 4 opponent
