@@ -115,7 +115,8 @@ def steady_state_runs(torch, ranks, step, K, W, repeats=5, spin_s=0.3, profile=F
     for r in range(repeats):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ranks.barrier()
-        if profile and r == 0:
+        step()                        # untimed pre-roll: the GPU is busy when ev0 fires, so the K timed steps run back
+        if profile and r == 0:        # to back from the first one (an idle GPU adds its launch latency to step 1)
             torch.cuda.profiler.start()
         ev0.record()
         for _ in range(K):

@@ -704,13 +704,16 @@ OTH_DEV void emit_dense(const EnvRegs<S> &e, bool active, bool zero_obs, bool ze
 template <int S>
 OTH_DEV void load_env(EnvRegs<S> &e, const oth_state &s, i64 i, i64 B) {
     constexpr int W = Geo<S>::W;
+    // ctr and meta first: they are needed first (the Philox draw depends on ctr alone, the terminated check on meta),
+    // and a warp's first wait at the top of k_step was the LAST of five loads (profiles/r03a: 35 % of the
+    // long-scoreboard samples sat on the first use of ctr)
+    e.ctr = s.ctr[i];
+    e.meta = s.meta[i];
     BB_FOR(k) {
+        e.legal.w[k] = s.legal[k * B + i];
         e.black.w[k] = s.black[k * B + i];
         e.white.w[k] = s.white[k * B + i];
-        e.legal.w[k] = s.legal[k * B + i];
     }
-    e.meta = s.meta[i];
-    e.ctr = s.ctr[i];
 }
 template <int S>
 OTH_DEV void store_env(const EnvRegs<S> &e, const oth_state &s, i64 i, i64 B) {
@@ -881,6 +884,10 @@ template <int S, int SRC, bool PACKED_ONLY>
 OTH_DEV void step_one_env(const StepParams &p, EnvRegs<S> &e, i64 i, i64 ext_action, bool &zero_obs) {
     StepResult r;
     r.reward = 0; r.done = 1; r.winner = 0; r.action = -1;
+    // in-kernel random policy: the draw depends on ctr alone, so it is computed BEFORE anything waits for meta or the
+    // bitboards (wasted only for finished envs, which do not advance ctr)
+    u32 rnd = 0;
+    if (SRC == OTH_ACT_RANDOM) rnd = philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr);
     if (e.meta & OTH_META_TERMINATED) {
         zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
         r.winner = meta_winner(e.meta);                    // its result stays readable (env.winner, othello.py:240)
@@ -888,7 +895,8 @@ OTH_DEV void step_one_env(const StepParams &p, EnvRegs<S> &e, i64 i, i64 ext_act
         i64 action = -1;
         const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73
         if (opening || SRC == OTH_ACT_RANDOM) {
-            action = random_pick<S>(e.legal, philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr));
+            if (SRC != OTH_ACT_RANDOM) rnd = philox_draw(p.keys, p.base + i, OTH_STREAM_ENV, e.ctr);
+            action = random_pick<S>(e.legal, rnd);
             e.ctr++;
             if (opening) e.meta += 1u << OTH_META_RANDCNT_SHIFT;
         } else if (SRC == OTH_ACT_GREEDY) {

@@ -18,5 +18,5 @@ except Exception as e: print(sys.argv[2], "FAILED", e)
 PY
 }
 run head_main X=1 $H
+run head_driver X=1 python bench.py --gpus 1 --steps 20 --warmup 5 --no-cpu-baseline --e2e-steps 3
 run sizes_main X=1 $Z
-run sizes_nibslab0 OTH_LIB_DIR=_lib_nibslab0 $Z
