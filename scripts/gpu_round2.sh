@@ -5,6 +5,7 @@ TAG=$1
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,driver_version,clocks.max.sm,clocks.max.mem,power.limit --format=csv > $OUT/gpu.txt 2>&1
+echo "== smoke"; python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $OUT/smoke.log
 echo "== pytest -m gpu"; timeout 1500 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -6 $OUT/pytest_gpu.log
 echo "== bench (driver command)"; timeout 600 python bench.py --gpus 1 --steps 20 --warmup 5 > $OUT/bench_driver.json 2> $OUT/bench_driver.err; echo "rc=$?"; tail -3 $OUT/bench_driver.err
 echo "== bench (2000 steps)"; timeout 600 python bench.py --steps 2000 --warmup 100 --no-cpu-baseline > $OUT/bench_2000.json 2> $OUT/bench_2000.err; echo "rc=$?"
@@ -22,5 +23,11 @@ for f in sorted(glob.glob(sys.argv[1]+"/bench_*.json")):
     except Exception as e:
         print(os.path.basename(f), "FAILED", e)
 PY
+echo "== ncu launch list of the timed region (headline)"
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $OUT/launches_timed_region.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 --profile-timed-region > $OUT/ncu_launches_timed.log 2>&1; echo "rc=$?"
+echo "== ncu launch list (whole short run)"
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 > $OUT/ncu_launches.log 2>&1; echo "rc=$?"
+echo "== ncu full of the headline kernel"
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:k_step -s 19 -c 1 -o $OUT/prof_step_8 python scripts/profile_targets.py step --size 8 > $OUT/ncu_full.log 2>&1; echo "rc=$?"
 echo "== ncu counters"; bash scripts/gpu_counts.sh $TAG
 ls $OUT
