@@ -32,6 +32,13 @@ def run_tournament(args):
     first = ranks.rank * games
     int_peak, sms = common.int32_peak(torch, ranks)
     counts = common.int_counts() or {}
+    nodes = {}
+    try:
+        import json
+        import os
+        nodes = json.load(open(os.path.join(common.ROOT, "profiles", "search_nodes.json")))
+    except (OSError, ValueError):
+        pass
 
     def launch(black, white, tally):
         rollout(games, _label(black), _label(white), board_size=8, initial_rand_steps=10, seed=0, env_id_base=first,
@@ -75,8 +82,12 @@ def run_tournament(args):
             rows[name].update(common.int_fraction({"int_thread_inst_per_unit": c["int_thread_inst_per_unit"],
                                                    "source_digest": c.get("source_digest"), "source": c.get("source")},
                                                   per_gpu_plies, int_peak))
-            if c.get("nodes_per_ply"):
-                rows[name]["search_nodes_per_s"] = rows[name]["outer_plies_per_s"] * c["nodes_per_ply"]
+        sn = nodes.get(name)
+        if sn:                                                      # profiles/search_nodes.json (counted on the GPU)
+            rows[name]["search_nodes_per_ply"] = sn["nodes_per_ply"]
+            rows[name]["search_nodes_per_s"] = rows[name]["outer_plies_per_s"] * sn["nodes_per_ply"]
+            if rows[name].get("int_thread_inst_per_unit"):
+                rows[name]["int_thread_inst_per_search_node"] = rows[name]["int_thread_inst_per_unit"] / sn["nodes_per_ply"]
     clocks = sampler.stop(t_h0 + 0.2, time.perf_counter())
     r = rows[main_name]
 

@@ -38,6 +38,6 @@ else:
     for _ in range(2):
         tally, _ = rollout(a.games, black, white, board_size=a.size, initial_rand_steps=10, seed=0)
     torch.cuda.synchronize()
-    t = [int(x) for x in tally.tolist()]
-    print(json.dumps({"target": "rollout", "pairing": a.pairing, "games": a.games, "units_per_launch": t[3] // 2,
-                      "plies_per_launch": t[3] // 2, "launches": 2}))
+    t = [int(x) for x in tally.tolist()]            # every rollout() call returns a fresh tally: ONE launch's plies
+    print(json.dumps({"target": "rollout", "pairing": a.pairing, "games": a.games, "units_per_launch": t[3],
+                      "plies_per_launch": t[3], "launches": 2}))
