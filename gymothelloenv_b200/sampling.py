@@ -144,8 +144,9 @@ class ChoiceStore(object):
         """choices_batch for flat sample indices i = t * num_envs + b (the order of `.view(-1, ...)` in
         feed_forward_generator, storage.py:127-145) -> int64 [W, len(indices)], ready for evaluate_actions."""
         idx = torch.as_tensor(indices, dtype=torch.int64, device=self.data.device)
-        flat = self.data.permute(1, 0, 2).reshape(self.words, self.num_steps * self.num_envs)
-        return flat.index_select(1, idx).contiguous()
+        t = torch.div(idx, self.num_envs, rounding_mode="floor")
+        b = idx - t * self.num_envs
+        return self.data[t, :, b].t().contiguous()               # [M, W] gathered rows -> [W, M]; the store is not copied
 
     def as_lists(self, indices):
         """The reference's representation (lists of ascending action ids), for tests and debugging."""
