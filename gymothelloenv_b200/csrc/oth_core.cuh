@@ -303,8 +303,7 @@ OTH_DEV BB<Geo<S>::W> legal(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp) 
 //   x = O | ~m ; t = x + 1 : the +1 carry ripples through every non-ray bit and through the
 //   contiguous opponent discs at the start of the ray and stops on the first ray cell that
 //   is not an opponent disc; t & ~x is that cell.  If it holds an own disc the run below it
-//   is bracketed, and the run is exactly the ray cells the carry cleared: flipped = m & O & ~t
-//   (no second 64-bit subtraction; k_step<8> went from 53 to 44 registers with it).
+//   is bracketed (ray_stop1 returns that closing disc, else 0).
 // The four rays towards lower indices are the same computation on bit-reversed boards.
 // Rays are mv * pattern (mv is a power of two, so the 64-bit IMADs are shifts that run on
 // the FMA pipe instead of the saturated ALU pipe); ray cells past the last board bit hold
@@ -321,10 +320,6 @@ struct GeoRays {
     static constexpr u64 e = geo_ray_pattern(S, 1), s = geo_ray_pattern(S, S);
     static constexpr u64 se = geo_ray_pattern(S, S + 1), sw = geo_ray_pattern(S, S - 1);
 };
-#ifndef OTH_FLIPS_STOP_MUL
-#define OTH_FLIPS_STOP_MUL 1    // 0: the round-1 form (compare + select per ray), kept for A/B timing
-#endif
-#if OTH_FLIPS_STOP_MUL
 // the closing own disc of one ray (0 if the run is not bracketed): see above
 OTH_DEV u64 ray_stop1(u64 m, u64 P, u64 O) {
     const u64 x = O | ~m;
@@ -354,36 +349,8 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
     const u64 up = flips1_half<S>(mvr, mv, __brevll(P), __brevll(O), __brevll(Oi));      // rays towards lower indices
     return up | __brevll(dn_rev);
 }
-#else
-OTH_DEV u64 ray_flips1(u64 m, u64 P, u64 O) {
-    const u64 x = O | ~m;
-    const u64 t = x + 1ull;
-    const u64 stop = t & ~x & P;                       // 0 or the single closing own disc
-    return stop != 0ull ? (m & O & ~t) : 0ull;         // ray cells the carry rippled through (all opponent discs)
-}
-template <int S>
-OTH_DEV u64 flips1_up(u64 mv, u64 P, u64 O, u64 Oi) {
-    u64 f = ray_flips1(mv * GeoRays<S>::e, P, Oi);
-    f |= ray_flips1(mv * GeoRays<S>::s, P, O);
-    f |= ray_flips1(mv * GeoRays<S>::se, P, Oi);
-    f |= ray_flips1(mv * GeoRays<S>::sw, P, Oi);
-    return f;
-}
-template <int S>
-OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
-    static_assert(Geo<S>::W == 1, "single-word boards only");
-    const u64 Oi = O & GeoWord<S, 0>::inner;
-    const u64 up = flips1_up<S>(mv, P, O, Oi);
-    const u64 dn = flips1_up<S>(__brevll(mv), __brevll(P), __brevll(O), __brevll(Oi));
-    return up | __brevll(dn);
-}
-
-#endif
 
 // ---- multi-word boards: flips by carry propagation -------------------------------------
-#ifndef OTH_RAY_PROGRESSION
-#define OTH_RAY_PROGRESSION 0   // 1: progression ray masks; measured 1-3 % SLOWER than the variable shift (profiles/r03e_experiments.md)
-#endif
 // whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
 template <int W> OTH_DEV BB<W> bb_shl_var(const BB<W> &x, int a) {
     const int q = a >> 6, b = a & 63;
@@ -420,7 +387,8 @@ template <int S, int D> OTH_DEV BB<Geo<S>::W> geo_ray() {
     if constexpr (Geo<S>::W > 3) r.w[3] = GeoRayWord<S, D, 3>::v;
     return r;
 }
-// one ray with mask m (cells above the move, nearest first): see ray_flips1
+// one ray with mask m (cells above the move, nearest first): the multi-word form of ray_stop1 -- the flipped run is
+// the ray cells the carry cleared, m & O & ~t, when the closing cell holds an own disc
 template <int W> OTH_DEV BB<W> ray_flips(const BB<W> &m, const BB<W> &P, const BB<W> &O) {
     BB<W> x;
     BB_FOR(i) x.w[i] = O.w[i] | ~m.w[i];
@@ -430,45 +398,6 @@ template <int W> OTH_DEV BB<W> ray_flips(const BB<W> &m, const BB<W> &P, const B
     const bool closed = any(stop);
     BB<W> r;
     BB_FOR(i) r.w[i] = closed ? (m.w[i] & O.w[i] & ~t.w[i]) : 0ull;   // ray cells the carry rippled through
-    return r;
-}
-// Ray masks without a variable whole-board shift.  The carry trick only needs the ray's cells to be the arithmetic
-// progression a + D, a + 2D, ... (it may run on past the ray's end: the ripple stops at the first progression cell
-// that is not an inner-column opponent disc, and padding bits hold neither colour), so
-//     ray(a, D) = (PROG_D << (a mod D)) & above(a)
-// PROG_D = every D-th bit of the W words (compile time); a mod D <= 16 < 32, so the shift is ONE funnel shift per
-// 32-bit half (2W SHF, no selects); above(a) = the bits higher than a, shared by the three rays of a half.  This
-// replaced bb_shl_var (a 64-bit variable shift per word plus a W x W select network): S = 12 2139 -> see profiles/.
-constexpr u64 geo_word_prog(int D, int wi) {
-    u64 m = 0;
-    for (int b = 0; b < 64; b++)
-        if ((wi * 64 + b) % D == 0) m |= 1ull << b;
-    return m;
-}
-template <int D, int WI> struct GeoProgWord { static constexpr u64 v = geo_word_prog(D, WI); };
-template <int D, int W> OTH_DEV BB<W> geo_prog() {
-    BB<W> r;
-    r.w[0] = GeoProgWord<D, 0>::v;
-    if constexpr (W > 1) r.w[1] = GeoProgWord<D, 1>::v;
-    if constexpr (W > 2) r.w[2] = GeoProgWord<D, 2>::v;
-    if constexpr (W > 3) r.w[3] = GeoProgWord<D, 3>::v;
-    return r;
-}
-// whole-board shift towards higher bit indices by 0 <= r < 32
-template <int W> OTH_DEV BB<W> bb_shl_lt32(const BB<W> &x, int r) {
-    u32 h[2 * W], o[2 * W];
-    BB_FOR(i) { h[2 * i] = (u32)x.w[i]; h[2 * i + 1] = (u32)(x.w[i] >> 32); }
-#pragma unroll
-    for (int j = 0; j < 2 * W; j++) o[j] = __funnelshift_l(j > 0 ? h[j > 0 ? j - 1 : 0] : 0u, h[j], r);
-    BB<W> y;
-    BB_FOR(i) y.w[i] = (u64)o[2 * i] | ((u64)o[2 * i + 1] << 32);
-    return y;
-}
-// bits strictly above the single bit mv (mv == 0: none)
-template <int W> OTH_DEV BB<W> bb_above(const BB<W> &mv) {
-    const BB<W> below = bb_sub<W>(mv, bb_one<W>(1ull));
-    BB<W> r;
-    BB_FOR(i) r.w[i] = ~(mv.w[i] | below.w[i]);
     return r;
 }
 // the four rays towards higher bit indices from cell a (mv = its bit): east needs no ray mask -- the
@@ -481,16 +410,11 @@ OTH_DEV BB<Geo<S>::W> flips_up(int a, const BB<Geo<S>::W> &mv, const BB<Geo<S>::
     const BB<W> sum = bb_add<W>(Oi, first);
     const BB<W> land = andnot(sum, Oi) & P;
     BB<W> f = bb_select(any(land), andnot(Oi, sum), bb_zero<W>());   // the discs the carry rippled through
-#if OTH_RAY_PROGRESSION
-    const BB<W> above = bb_above<W>(mv);
-    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S, W>(), a % S) & above, P, O);
-    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S + 1, W>(), a % (S + 1)) & above, P, Oi);
-    f = f | ray_flips<W>(bb_shl_lt32<W>(geo_prog<S - 1, W>(), a % (S - 1)) & above, P, Oi);
-#else
+    // (ray masks as (every D-th bit << a mod D) & above(a) avoid this variable whole-board shift but measured 1-3 %
+    // slower: profiles/r03e_experiments.md)
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S>(), a), P, O);
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S + 1>(), a), P, Oi);
     f = f | ray_flips<W>(bb_shl_var<W>(geo_ray<S, S - 1>(), a), P, Oi);
-#endif
     return f;
 }
 

@@ -21,10 +21,6 @@ static inline int __popcll(unsigned long long x) { return __builtin_popcountll(x
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline int __ffsll(long long x) { return __builtin_ffsll(x); }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
-static inline unsigned __funnelshift_l(unsigned lo, unsigned hi, unsigned s) {
-    s &= 31u;
-    return s ? ((hi << s) | (lo >> (32u - s))) : hi;
-}
 static inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((unsigned long long)a * b) >> 32); }
 using std::max;
 using std::min;
