@@ -33,7 +33,9 @@ struct WarpStageT {
 };
 template <int S>
 struct WarpStageT<S, true> {
-    uint4 nib[NIB_ROWS][32][Geo<S>::W];     // [row][env lane][16 nibbles per 64 cells, one per byte]
+    // [row][env lane][16 nibbles per 64 cells, one per byte]; the slab writers reuse the same bytes.  10x10 gets one
+    // more row (1 KB per warp) so that TWO output slabs (obs + mask, 2 x 3200 B) fit: the bulk-store path needs both.
+    uint4 nib[NIB_ROWS + (S == 10 ? 1 : 0)][32][Geo<S>::W];
 };
 template <int S>
 using WarpStage = WarpStageT<S>;
@@ -836,6 +838,28 @@ OTH_DEV void fast8_full_eo(void *base, i64 env0, const uint4 *pos_rows, const ui
     }
 }
 
+// Finished warp slab -> global memory as ONE bulk async copy (cp.async.bulk shared::cta -> global) issued by lane 0,
+// instead of ceil(2N/32) LDS.128 + STG.128 pairs per lane.  Every lane fences its generic-proxy shared stores towards
+// the async proxy, the warp synchronises, lane 0 issues the copy and commits the group.  The slab may be rewritten
+// (and the warp may exit) only after slab_bulk_wait().
+template <int S>
+OTH_DEV void slab_bulk_store(const unsigned char *slab, void *base, i64 env0, int lane) {
+    constexpr int BYTES = 32 * Geo<S>::N;
+    static_assert(BYTES % 16 == 0, "bulk copies move multiples of 16 bytes");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) {
+        char *dst = reinterpret_cast<char *>(base) + env0 * (i64)Geo<S>::N;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                     :: "l"(dst), "r"((u32)__cvta_generic_to_shared(slab)), "n"(BYTES) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+}
+OTH_DEV void slab_bulk_wait(int lane) {
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncwarp();
+}
+
 // The headline output set with everything decided at compile time (oth_step dispatches here when it applies):
 // int8 `board` observation + dense legal mask, full warps only; S == 8 uses the even/odd nibble stage, the other
 // even sizes the slab writer.
@@ -860,9 +884,20 @@ OTH_DEV void emit_board_mask_fast(const EnvRegs<S> &e, bool zero, const oth_outp
     } else {
         static_assert(sizeof(st.nib) >= 32 * Geo<S>::N, "slab must fit the warp stage");
         unsigned char *base = reinterpret_cast<unsigned char *>(&st.nib[0][0][0]);
-        {
-            // (a nibble-staged expansion with LDS.U8 extraction, as in the 8x8 writer, measured 1-4 % slower here:
-            // profiles/r03e_experiments.md)
+        // (a nibble-staged expansion with LDS.U8 extraction, as in the 8x8 writer, measured 1-4 % slower here:
+        // profiles/r03e_experiments.md)
+        // bulk async stores where BOTH slabs (obs + mask) fit the stage and a slab is at least 3 KB (10x10, 12x12):
+        // measured -3.3 % on 12x12; +2.7 % on 6x6 (1.1 KB copies do not pay for fence + wait) and neutral with a
+        // single slab that must be drained between the two copies (profiles/r03q_bulk_store.md)
+        constexpr int SLAB = 32 * Geo<S>::N;
+        constexpr bool BULK = 2 * SLAB <= (int)sizeof(WarpStage<S>) && SLAB >= 3072;
+        if constexpr (BULK) {
+            slab_expand<S, true>(base, lane, pos, neg);
+            slab_bulk_store<S>(base, out.obs, warp_env0, lane);
+            slab_expand<S, false>(base + SLAB, lane, lg, lg);
+            slab_bulk_store<S>(base + SLAB, out.legal_mask, warp_env0, lane);
+            slab_bulk_wait(lane);
+        } else {
             slab_expand<S, true>(base, lane, pos, neg);
             __syncwarp();
             slab_copy<S>(base, out.obs, warp_env0, lane);
