@@ -107,13 +107,13 @@ __device__ int policy_pick(int kind, int depth, const BB<Geo<S>::W> &own, const 
     if (kind == OTH_POLICY_MAXIMIN || !DEEP) {
         if (depth == 2) return MaxiMin<S, 2>::pick(own, opp, moves);
         if (depth == 3) return MaxiMin<S, 3>::pick(own, opp, moves);
-        if (depth == 4 || !DEEP) return MaxiMin<S, 4>::pick(own, opp, moves);   // !DEEP: unreachable for depth > 4
+        if (depth == 4) return MaxiMin<S, 4>::pick(own, opp, moves);
     }
     if constexpr (DEEP) {
         unsigned long long nodes = 0;
         return search_pick<S>(own, opp, moves, depth, true, nodes);
     }
-    return -1;
+    return -1;      // a depth this instantiation does not search: never a silently shallower move (an invalid action)
 }
 
 #ifndef OTH_HOST_EMUL

@@ -18,7 +18,7 @@ def _raw_step(env, out, policy_src=_cabi.ACT_RANDOM, actions=None):
                              C.c_void_p(torch.cuda.current_stream(env.device).cuda_stream)), "oth_step")
 
 
-@pytest.mark.parametrize("S,B", [(8, 1024), (8, 1000), (6, 512), (10, 384), (7, 256)])
+@pytest.mark.parametrize("S,B", [(8, 1024), (8, 1000), (6, 512), (10, 384), (7, 256), (12, 256), (4, 128), (14, 128), (16, 128)])
 def test_packed_record_equals_separate_arrays_and_fast_equals_general(S, B):
     """Two envs on the same seed: A steps through VecOthelloEnv (packed record only -> the FAST kernel when B is a
     multiple of 128 and S is even), B through the raw C ABI with EVERY separate array plus the packed record (the
