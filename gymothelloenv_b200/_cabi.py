@@ -38,6 +38,7 @@ OBS_NONE, OBS_BOARD, OBS_BOARD_MASK, OBS_PLANES4, OBS_PLANES3, OBS_ABSOLUTE = 0,
 OBS_PLANES = {OBS_NONE: 0, OBS_BOARD: 1, OBS_BOARD_MASK: 2, OBS_PLANES4: 4, OBS_PLANES3: 3, OBS_ABSOLUTE: 1}
 DTYPE_I8, DTYPE_F32 = 0, 1
 ACT_EXTERNAL, ACT_RANDOM, ACT_GREEDY = 0, 1, 2
+ACTION_HOLD = -(1 << 63)          # OTH_ACTION_HOLD: the env sits this ply out
 POLICY_RANDOM, POLICY_GREEDY, POLICY_MAXIMIN, POLICY_ALPHABETA = 0, 1, 2, 3
 MAX_SEARCH_DEPTH = 8
 SEARCH_PRUNE, SEARCH_COOPERATIVE = 1, 2

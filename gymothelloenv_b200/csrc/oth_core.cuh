@@ -350,6 +350,85 @@ OTH_DEV u64 flips1(u64 mv, u64 P, u64 O) {
     return up | __brevll(dn_rev);
 }
 
+// ---- single-word boards: the flip count of EVERY cell at once (bit-sliced) --------------
+// GreedyPolicy and the last ply of MaxiMinPolicy.search only need the LARGEST number of discs any one move turns
+// (simple_policies.py:69-92; :127-137 at depth 1: value = own count + flips + 1, resp. opponent count - flips).
+// Instead of one flips1() per move, each of the 8 directions is walked once for all cells: t_k = the k-th disc of an
+// opponent run that starts next to an own disc; a move on the cell behind t_k turns exactly k discs in that direction.
+// The run length k (1..S-2) of a cell is kept as three bit planes; the eight directions are added with bit-sliced
+// adders -- opposite directions first: a line through a cell holds at most S-1 other cells and every bracketed run
+// needs its closing disc, so the two sums together stay <= S-2 and still fit three planes; four such sums
+// (<= 4(S-2) <= 24) fit five -- and the maximum over a set of cells falls out of the planes from the top bit down.
+// About 400 instructions whatever the number of moves (one flips1 + popcount per move costs ~125), and no loop whose
+// trip count differs between the lanes of a warp.  Planes are only meaningful on EMPTY cells.
+struct FlipPlanes { u64 c[5]; };
+template <int D, bool UP> OTH_DEV u64 sh1(u64 x) { return UP ? (x << D) : (x >> D); }
+OTH_DEV u64 maj3(u64 a, u64 b, u64 c) { return (a & b) | (c & (a | b)); }
+// one direction: bit planes of the run length seen from the cell behind the run
+template <int S, int D, bool UP>
+OTH_DEV void run_planes1(u64 P, u64 m, u64 &b0, u64 &b1, u64 &b2) {
+    constexpr int R = S - 2;
+    u64 t[6];
+    t[0] = sh1<D, UP>(P) & m;
+#pragma unroll
+    for (int k = 1; k < 6; k++) t[k] = k < R ? (sh1<D, UP>(t[k - 1]) & m) : 0ull;
+    b0 = sh1<D, UP>(t[0] | t[2] | t[4]);
+    b1 = sh1<D, UP>(t[1] | t[2] | t[5]);
+    b2 = sh1<D, UP>(t[3] | t[4] | t[5]);
+}
+// both directions of one axis, added (sum <= S-2: no fourth plane)
+template <int S, int D>
+OTH_DEV void axis_planes1(u64 P, u64 m, u64 *s) {
+    u64 a0, a1, a2, b0, b1, b2;
+    run_planes1<S, D, true>(P, m, a0, a1, a2);
+    run_planes1<S, D, false>(P, m, b0, b1, b2);
+    const u64 c0 = a0 & b0;
+    s[0] = a0 ^ b0;
+    s[1] = a1 ^ b1 ^ c0;
+    s[2] = a2 ^ b2 ^ maj3(a1, b1, c0);
+}
+template <int S>
+OTH_DEV FlipPlanes flip_planes1(u64 P, u64 O) {
+    static_assert(Geo<S>::W == 1, "single-word boards only");
+    const u64 Oi = O & GeoWord<S, 0>::inner;
+    u64 h[3], v[3], d[3], e[3];
+    axis_planes1<S, 1>(P, Oi, h);
+    axis_planes1<S, S>(P, O, v);
+    axis_planes1<S, S + 1>(P, Oi, d);
+    axis_planes1<S, S - 1>(P, Oi, e);
+    u64 x[4], y[4], c;                                    // x = h + v, y = d + e: four planes each
+    x[0] = h[0] ^ v[0]; c = h[0] & v[0];
+    x[1] = h[1] ^ v[1] ^ c; c = maj3(h[1], v[1], c);
+    x[2] = h[2] ^ v[2] ^ c; x[3] = maj3(h[2], v[2], c);
+    y[0] = d[0] ^ e[0]; c = d[0] & e[0];
+    y[1] = d[1] ^ e[1] ^ c; c = maj3(d[1], e[1], c);
+    y[2] = d[2] ^ e[2] ^ c; y[3] = maj3(d[2], e[2], c);
+    FlipPlanes f;                                         // x + y: five planes
+    f.c[0] = x[0] ^ y[0]; c = x[0] & y[0];
+    f.c[1] = x[1] ^ y[1] ^ c; c = maj3(x[1], y[1], c);
+    f.c[2] = x[2] ^ y[2] ^ c; c = maj3(x[2], y[2], c);
+    f.c[3] = x[3] ^ y[3] ^ c; f.c[4] = maj3(x[3], y[3], c);
+    return f;
+}
+// the largest count among the cells of `cand`; cand shrinks to the cells that reach it
+OTH_DEV int planes_max(const FlipPlanes &f, u64 &cand) {
+    int v = 0;
+#pragma unroll
+    for (int p = 4; p >= 0; p--) {
+        const u64 t = cand & f.c[p];
+        if (t != 0ull) { cand = t; v |= 1 << p; }
+    }
+    return v;
+}
+// legal moves of P (as legal1) and the most discs any of them turns (0 when there is no move)
+template <int S>
+OTH_DEV int max_flips1(u64 P, u64 O, u64 &moves) {
+    const FlipPlanes f = flip_planes1<S>(P, O);
+    moves = (f.c[0] | f.c[1] | f.c[2] | f.c[3] | f.c[4]) & ~(P | O) & GeoWord<S, 0>::full;
+    u64 cand = moves;
+    return planes_max(f, cand);
+}
+
 // ---- multi-word boards: flips by carry propagation -------------------------------------
 // whole-board shift towards higher bit indices by a VARIABLE distance 0 <= a < 64*W
 template <int W> OTH_DEV BB<W> bb_shl_var(const BB<W> &x, int a) {
@@ -676,6 +755,18 @@ OTH_DEV int random_pick(const BB<Geo<S>::W> &moves, u32 rnd) {
 template <int S>
 OTH_DEV int greedy_pick(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp, BB<Geo<S>::W> moves) {
     constexpr int W = Geo<S>::W;
+    if constexpr (W == 1) {
+        // all moves at once (flip_planes1).  A cached list that names OCCUPIED cells can only come from
+        // set_board_state without a refresh of the list (othello.py:380-389 keeps possible_moves): the loop below
+        // reproduces update_board on such cells.
+        if ((moves.w[0] & (own.w[0] | opp.w[0])) == 0ull) {
+            if (moves.w[0] == 0ull) return -1;
+            const FlipPlanes f = flip_planes1<S>(own.w[0], opp.w[0]);
+            u64 cand = moves.w[0];
+            planes_max(f, cand);
+            return __ffsll((long long)cand) - 1;           // np.argmax: the first (lowest) of the best moves
+        }
+    }
     int best = -1, best_cnt = -1;
     while (any(moves)) {
         int a = lowest_bit(moves);
@@ -695,6 +786,11 @@ struct MaxiMin {
         constexpr int W = Geo<S>::W;
         if constexpr (D == 0) {
             return popc(me_is_pl ? pl : op);
+        } else if constexpr (D == 1 && W == 1) {          // children are leaves: every move scored at once
+            u64 moves;
+            const int k = max_flips1<S>(pl.w[0], op.w[0], moves);
+            if (moves == 0ull) return popc(me_is_pl ? pl : op);
+            return me_is_pl ? popc(pl) + k + 1 : popc(op) - k;
         } else {
             BB<W> moves = legal<S>(pl, op);
             if (!any(moves)) return popc(me_is_pl ? pl : op);

@@ -926,6 +926,8 @@ OTH_DEV void step_one_env(const StepParams &p, EnvRegs<S> &e, i64 i, i64 ext_act
     if (e.meta & OTH_META_TERMINATED) {
         zero_obs = true;                                   // finished env: no-op ('over', ppo_run_self_play.py:274)
         r.winner = meta_winner(e.meta);                    // its result stays readable (env.winner, othello.py:240)
+    } else if (SRC == OTH_ACT_EXTERNAL && ext_action == OTH_ACTION_HOLD) {
+        r.done = 0;                                        // sits this ply out: state as it was, outputs re-emitted
     } else {
         i64 action = -1;
         const bool opening = meta_rand_cnt(e.meta) < meta_rand_max(e.meta);   // othello.py:70-73

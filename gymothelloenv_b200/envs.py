@@ -67,7 +67,6 @@ class _RuleBaseGames(object):
         B, N = self.num_processes, v.num_cells
         per = int(num_games) // B
         wins = torch.zeros((B,), dtype=torch.int64, device=self.device)
-        ones = torch.ones((B, 1), dtype=torch.float32, device=self.device)
         for g in range(per):
             pin = None
             if protagonists is not None:
@@ -83,19 +82,32 @@ class _RuleBaseGames(object):
             try:
                 v.refresh_outputs()
                 P = self.protagonist.clone()
-                for ply in range(N - 4):                                 # every valid ply fills one cell
-                    turn = v.player_turn.clone()
+                hold = torch.full((B,), _cabi.ACTION_HOLD, dtype=torch.int64, device=self.device)
+                ones = torch.ones((B, 1), dtype=torch.float32, device=self.device)
+                # The reference's workers run at their own pace: each plays the scripted side's plies on its own and
+                # only then asks the learner (ppo_run_self_play.py:381-387), and Envs.test (envs.py:233-250) serves
+                # one request of EVERY worker per policy.act.  In lockstep: while some game waits for the scripted
+                # side, those games move and the others are held (OTH_ACTION_HOLD); once every running game waits
+                # for the learner, one act on the whole batch (row i = env i, as in the reference) moves them all.
+                # About half as many forward passes as one per ply.
+                for rounds in range(N * N + 1):                          # every round places a disc in >= 1 running game
+                    if rounds == N * N:
+                        raise RuntimeError("test games did not finish")
                     live = ~v.terminated()
-                    with torch.no_grad():
-                        _, actions, _, _ = policy.act(v.obs, ex_hiddens, ones, self._choices_arg(v.legal_mask))
-                    a = self._as_dev(actions, torch.int64)
-                    scripted = v.policy_actions(name)
-                    mine = turn == P
-                    v.step(torch.where(mine, a, scripted))
-                    sign = torch.where(mine, 1.0, -1.0)
-                    wins += (live & v.done & (v.reward * sign > 0)).to(torch.int64)   # :432-439
-                    if ply % 8 == 7 and bool(v.terminated().all().item()):
+                    theirs = live & (v.player_turn != P)
+                    n_theirs, n_live = (int(x) for x in torch.stack((theirs.sum(), live.sum())).tolist())   # one sync
+                    if n_live == 0:
                         break
+                    if n_theirs > 0:
+                        moved, sign = theirs, -1.0
+                        v.step(torch.where(theirs, v.policy_actions(name), hold))
+                    else:
+                        with torch.no_grad():
+                            _, actions, _, _ = policy.act(v.obs, ex_hiddens, ones, self._choices_arg(v.legal_mask))
+                        self.test_policy_calls += 1
+                        moved, sign = live, 1.0
+                        v.step(torch.where(live, self._as_dev(actions, torch.int64), hold))
+                    wins += (moved & v.done & (v.reward * sign > 0)).to(torch.int64)   # :432-439
             finally:
                 v.initial_rand_steps = saved_rand                        # :440
         return per * B, int(wins.sum().item())
@@ -172,6 +184,7 @@ class Envs(_RuleBaseGames):
         self._c_tr_choice_out = _cabi.OthOutputs(None, _cabi.ptr(self._tr_choices_u8), None, None, None, None, None,
                                                  _cabi.OBS_NONE, _cabi.DTYPE_I8)
         self.policy_calls = 0
+        self.test_policy_calls = 0            # policy.act calls made by test(): one per learner ply, not one per ply
 
     # ------------------------------------------------------------------ envs.py:27-35
     def over(self):

@@ -176,6 +176,8 @@ class VecOthelloEnv(object):
         self.seed_value = int(seed) & 0xFFFFFFFFFFFFFFFF
         self._ctr.zero_()
 
+    HOLD = _cabi.ACTION_HOLD          # step(actions): the env sits this ply out
+
     def reset(self, where=None):
         """Resets every env (or those with where[i] True) and returns the observation tensor."""
         only = None
@@ -196,7 +198,9 @@ class VecOthelloEnv(object):
         """One ply in every env.
 
         actions: int64 CUDA tensor [B] (``env.step(a)``), or None with policy='random' |
-        'greedy' to let the kernel play the side to move (fused policy + step).
+        'greedy' to let the kernel play the side to move (fused policy + step).  An entry equal to
+        ``VecOthelloEnv.HOLD`` (OTH_ACTION_HOLD) leaves that env alone for this ply: state kept, outputs
+        re-emitted, reward 0, done False.
         Returns (obs, reward f32[B], done bool[B], info) with info = {'legal_mask',
         'player_turn', 'winner', 'actions'}; all CUDA tensors owned by the env and
         overwritten by the next call."""

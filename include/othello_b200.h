@@ -85,6 +85,10 @@ typedef struct oth_state {
 
 /* where oth_step takes its actions from */
 #define OTH_ACT_EXTERNAL 0   /* `actions` array, like env.step(a) */
+/* actions[i] == OTH_ACTION_HOLD: env i sits this ply out -- state untouched, outputs re-emitted, reward 0, done 0.
+ * The reference's workers each step at their own pace (ppo_run_self_play.py:371-441: a worker plays the scripted
+ * opponent's plies on its own and only then asks for an action); a lockstep batch needs a way to leave an env alone. */
+#define OTH_ACTION_HOLD (-0x7FFFFFFFFFFFFFFFLL - 1)
 #define OTH_ACT_RANDOM   1   /* in-kernel RandomPolicy (simple_policies.py:37-41), Philox stream */
 #define OTH_ACT_GREEDY   2   /* in-kernel GreedyPolicy (simple_policies.py:69-92) */
 
@@ -146,7 +150,8 @@ int oth_observe(oth_state st, int64_t B, int board_size, int flags, oth_outputs 
 /* One lockstep ply for every env: OthelloBaseEnv.step (othello.py:412-462) preceded by
  * SimpleOthelloEnv.step's random-opening override (othello.py:68-73).
  * action_source = OTH_ACT_EXTERNAL reads actions[i] (any int64: out-of-range or not in
- * the cached list = invalid move => sudden death or forfeited turn, othello.py:417-428).
+ * the cached list = invalid move => sudden death or forfeited turn, othello.py:417-428;
+ * OTH_ACTION_HOLD = leave this env alone).
  * Envs that are already terminated are a no-op reporting done=1, reward=0 and a zero
  * observation (the reference raises ValueError, othello.py:415-416; the batched
  * contract mirrors the worker's 'over' message, ppo_run_self_play.py:274). */

@@ -92,6 +92,30 @@ static void nth_batch(int64_t B, const uint64_t *legal_, const int32_t *n, int64
     }
 }
 
+// bit-sliced flip counts (flip_planes1 / max_flips1) next to the per-move flips1 + legal1 they replace
+template <int S>
+static void flipcount_batch(int64_t B, const uint64_t *own, const uint64_t *opp, int8_t *sliced, int8_t *per_move,
+                            uint64_t *moves_sliced, uint64_t *moves_legal1, int32_t *max_sliced) {
+    if constexpr (Geo<S>::W == 1) {
+        constexpr int N = Geo<S>::N;
+        for (int64_t i = 0; i < B; i++) {
+            const u64 P = own[i], O = opp[i];
+            const FlipPlanes f = flip_planes1<S>(P, O);
+            for (int a = 0; a < 64; a++) {
+                int c = 0;
+                for (int p = 0; p < 5; p++) c |= (int)((f.c[p] >> a) & 1ull) << p;
+                const bool empty = a < N && !(((P | O) >> a) & 1ull);
+                sliced[i * 64 + a] = (int8_t)(empty ? c : -1);
+                per_move[i * 64 + a] = (int8_t)(empty ? __popcll(flips1<S>(1ull << a, P, O)) : -1);
+            }
+            u64 mv;
+            max_sliced[i] = max_flips1<S>(P, O, mv);
+            moves_sliced[i] = mv;
+            moves_legal1[i] = legal1<S>(P, O);
+        }
+    }
+}
+
 #define DISPATCH(S_, CALL)                                                                                   \
     switch (S_) {                                                                                            \
     case 4: CALL(4); break; case 5: CALL(5); break; case 6: CALL(6); break; case 7: CALL(7); break;          \
@@ -131,6 +155,14 @@ int emul_search(int S, int64_t B, const uint64_t *black, const uint64_t *white, 
 }
 int emul_nth(int S, int64_t B, const uint64_t *legal_, const int32_t *n, int64_t *out) {
 #define CALL(N) nth_batch<N>(B, legal_, n, out)
+    DISPATCH(S, CALL)
+#undef CALL
+    return 0;
+}
+int emul_flipcount(int S, int64_t B, const uint64_t *own, const uint64_t *opp, int8_t *sliced, int8_t *per_move,
+                   uint64_t *moves_sliced, uint64_t *moves_legal1, int32_t *max_sliced) {
+    if (S > 8) return -1;
+#define CALL(N) flipcount_batch<N>(B, own, opp, sliced, per_move, moves_sliced, moves_legal1, max_sliced)
     DISPATCH(S, CALL)
 #undef CALL
     return 0;

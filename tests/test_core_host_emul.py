@@ -118,7 +118,7 @@ def test_random_games_match_oracle(emul, S, sudden, disk):
         raise AssertionError("games did not finish")
 
 
-@pytest.mark.parametrize("S,depths", [(4, (1, 2, 3, 4)), (6, (1, 2, 3)), (8, (1, 2, 3)), (9, (1, 2)), (10, (1, 2)),
+@pytest.mark.parametrize("S,depths", [(4, (1, 2, 3, 4)), (5, (1, 2, 3)), (6, (1, 2, 3)), (7, (1, 2, 3)), (8, (1, 2, 3)), (9, (1, 2)), (10, (1, 2)),
                                       (12, (1, 2)), (13, (1,)), (16, (1,))])
 def test_policy_picks_match_oracle(emul, S, depths):
     """greedy and maximin-k choices on positions reached by random play (first-occurrence ties included)."""
@@ -174,6 +174,28 @@ def test_alpha_beta_search_matches_oracle_maximin(emul, S, depths):
         orc.step(acts)
         ev.step(acts, F_SUDDEN)
     assert checked > 20
+
+
+@pytest.mark.parametrize("S", [4, 5, 6, 7, 8])
+def test_bit_sliced_flip_counts_equal_per_move_flips(emul, S):
+    """flip_planes1 / max_flips1 (every move scored at once: greedy and the last ply of the searches) against one
+    flips1 + popcount per cell and legal1, on ARBITRARY disc patterns -- sparse, dense, reachable or not."""
+    rng = np.random.RandomState(100 + S)
+    N, B = S * S, 6000
+    fill = rng.choice([0.15, 0.4, 0.7, 0.95], size=B)
+    cells = rng.rand(B, N)
+    colour = rng.rand(B, N) < rng.choice([0.2, 0.5, 0.8], size=(B, 1))
+    occupied = cells < fill[:, None]
+    weights = (np.uint64(1) << np.arange(N, dtype=np.uint64))
+    own = ((occupied & colour).astype(np.uint64) * weights).sum(1).astype(np.uint64)
+    opp = ((occupied & ~colour).astype(np.uint64) * weights).sum(1).astype(np.uint64)
+    sliced, per_move = np.zeros((B, 64), dtype=np.int8), np.zeros((B, 64), dtype=np.int8)
+    mv_s, mv_l, mx = np.zeros(B, dtype=np.uint64), np.zeros(B, dtype=np.uint64), np.zeros(B, dtype=np.int32)
+    assert emul.emul_flipcount(S, C.c_int64(B), _p(own), _p(opp), _p(sliced), _p(per_move), _p(mv_s), _p(mv_l), _p(mx)) == 0
+    assert np.array_equal(sliced, per_move)
+    assert np.array_equal(mv_s, mv_l)
+    assert np.array_equal(mx, per_move.max(1).clip(min=0))
+    assert per_move.max() >= min(2 * (S - 2), 8) and (mv_s != 0).mean() > 0.3      # the cases are not trivial
 
 
 def test_nth_set_bit(emul):

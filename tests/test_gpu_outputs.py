@@ -129,6 +129,56 @@ def test_step_host_packed_expands_to_the_dense_outputs(S):
     assert h2d == 2 * B and d2h == B * (24 * pk.words + 6)
 
 
+@pytest.mark.parametrize("S,B", [(8, 256), (8, 200), (6, 128), (10, 128), (7, 96)])
+def test_held_envs_sit_a_ply_out(S, B):
+    """actions[i] == OTH_ACTION_HOLD: env i keeps its state and re-emits its outputs (reward 0, done 0) while the
+    others move.  Per-env replay: env i of the held run after its k-th real move equals env i of a run in which every
+    env moves on every ply, after k plies (same start, same deterministic action rule)."""
+    free = VecOthelloEnv(B, board_size=S, seed=4, initial_rand_steps=0)
+    held = VecOthelloEnv(B, board_size=S, seed=4, initial_rand_steps=0)
+    free.reset()
+    held.reset()
+    keys = ("black", "white", "legal", "meta")
+
+    def snap(env):                                            # everything a step produces, (B, ...) per field
+        st = env.get_state()
+        d = {k: (st[k].t() if st[k].dim() == 2 else st[k]).cpu().numpy().copy() for k in keys}
+        d.update(obs=env.obs.cpu().numpy().copy(), mask=env.legal_mask.cpu().numpy().copy(),
+                 done=env.done.cpu().numpy().copy(), reward=env.reward.cpu().numpy().copy(),
+                 turn=env.player_turn.cpu().numpy().copy())
+        return d
+    hist_a, hist = [], []
+    for t in range(S * S):
+        a = free.policy_actions("greedy")                     # a deterministic function of the position
+        free.step(a)
+        hist_a.append(a.cpu().numpy().copy())
+        hist.append(snap(free))
+    hist_a = np.stack(hist_a)
+    hist = {k: np.stack([h[k] for h in hist]) for k in hist[0]}      # (T, B, ...)
+    rng = np.random.RandomState(S)
+    hold = torch.full((B,), _cabi.ACTION_HOLD, dtype=torch.int64, device="cuda")
+    moves = np.zeros(B, dtype=np.int64)                       # real moves each env of the held run has made
+    prev = snap(held)
+    for t in range(4 * S * S):
+        sit = rng.rand(B) < 0.5
+        term0 = held.terminated().cpu().numpy().astype(bool)
+        a = held.policy_actions("greedy")
+        held.step(torch.where(torch.from_numpy(sit).cuda(), hold, a))
+        cur = snap(held)
+        s_idx, m_idx = np.flatnonzero(sit & ~term0), np.flatnonzero(~sit & ~term0)
+        for k in keys + ("obs", "mask", "turn"):              # held: nothing moved, outputs re-emitted
+            assert np.array_equal(cur[k][s_idx], prev[k][s_idx]), (k, t)
+        assert not cur["done"][s_idx].any() and not cur["reward"][s_idx].any()
+        assert np.array_equal(a.cpu().numpy()[m_idx], hist_a[moves[m_idx], m_idx])
+        for k in hist:                                        # moved: exactly the free run's next ply of that env
+            assert np.array_equal(cur[k][m_idx], hist[k][moves[m_idx], m_idx]), (k, t)
+        moves[m_idx] += 1
+        prev = cur
+        if cur["done"].all() or held.terminated().all():
+            break
+    assert bool(held.terminated().all()) and moves.min() > 4
+
+
 def test_the_stub_in_integration_md_runs_as_written():
     """INTEGRATION.md section B is the binding a maintainer of the reference would copy: execute it verbatim."""
     import os

@@ -134,6 +134,9 @@ def test_rule_base_game_vs_oracle_and_random_opponent():
     games, wins = envs.test("greedy", per * B, None, protagonists=prot)
     want = rule_base_games(FakePolicy(S), "greedy", per, S, prot, disk_reward=True)
     assert (games, wins) == (per * B, int(want.sum()))
+    # one forward pass per LEARNER ply (envs.py:233-250 serves one request of every worker per act), not one per ply:
+    # a game has at most (S*S - 4) plies, about half of them the learner's
+    assert 0 < envs.test_policy_calls <= per * 0.6 * (S * S - 4)
     # 'rand' opponent + opening budget: statistical only (Philox vs numpy MT streams)
     envs = _mk(B, S, True, test_rand_steps=10)
     games, wins = envs.test("rand", 4 * B, None)
