@@ -71,6 +71,20 @@ class ClockSampler(object):
         for line in self.proc.stdout:
             self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
+    def wait_for(self, n=1, timeout=5.0, since=0.0):
+        """Blocks until `n` samples newer than `since` have arrived (nvidia-smi can take more than a second to print
+        its first line on a fresh box: a short bench used to end before it did and reported no clocks at all)."""
+        if self.proc is None:
+            return False
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < timeout:
+            if sum(1 for (t, _) in self.rows if t >= since) >= n:
+                return True
+            if self.proc.poll() is not None:
+                return False
+            time.sleep(0.01)
+        return False
+
     def stop(self, t0, t1):
         """Samples taken in [t0, t1] (the GPU is under the bench's own load for all of it)."""
         if self.proc is None:
@@ -103,12 +117,16 @@ def steady_state_runs(torch, ranks, step, K, W, repeats=5, spin_s=0.3, profile=F
         step()
     ranks.barrier()
     sampler = ClockSampler(ranks.local).start()
+    sampler.wait_for(1, timeout=5.0)                 # the sampler is up before the load starts
     t_spin = time.perf_counter()
     while True:
         for _ in range(64):
             step()
         torch.cuda.synchronize(ranks.dev)
-        if time.perf_counter() - t_spin >= spin_s:
+        dt = time.perf_counter() - t_spin
+        # at least spin_s, and until three clock samples were taken UNDER this load (bounded: 3 s)
+        if dt >= spin_s and (dt >= 3.0 or sampler.proc is None or
+                             sum(1 for (t, _) in sampler.rows if t >= t_spin + 0.1) >= 3):
             break
     t_host0 = t_spin + 0.1
     runs = []

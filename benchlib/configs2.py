@@ -67,6 +67,7 @@ def run_tournament(args):
                 "timed_runs_ms": runs}
 
     sampler = common.ClockSampler(ranks.local).start()
+    sampler.wait_for(1, timeout=5.0)
     t_h0 = time.perf_counter()
     main_name = args.pairing if args.pairing in PAIRINGS else "greedy_vs_maximin2"
     rows = {}
@@ -88,7 +89,7 @@ def run_tournament(args):
             rows[name]["search_nodes_per_s"] = rows[name]["outer_plies_per_s"] * sn["nodes_per_ply"]
             if rows[name].get("int_thread_inst_per_unit"):
                 rows[name]["int_thread_inst_per_search_node"] = rows[name]["int_thread_inst_per_unit"] / sn["nodes_per_ply"]
-    clocks = sampler.stop(t_h0 + 0.2, time.perf_counter())
+    clocks = sampler.stop(t_h0 + 0.05, time.perf_counter())
     r = rows[main_name]
 
     # e2e: host call -> fused tournament -> D2H of the tally (32 bytes); nothing else ever crosses PCIe

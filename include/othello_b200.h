@@ -69,8 +69,8 @@ typedef struct oth_state {
                                          (default: keep ppo_run_self_play.py:291-301's stale state in pass runs) */
 #define OTH_F_SEARCH_PER_THREAD 0x80   /* oth_rollout: every maximin decision by the per-thread DFS (no lane-cooperative
                                            search); same results, for A/B timing and cross-checks */
-#define OTH_F_SEARCH_SMALL_LISTS 0x40  /* oth_rollout, tests only: the lane-cooperative maximin search keeps at most 3 root
-                                           moves / 12 (move, reply) pairs, so its per-thread fallback runs constantly */
+#define OTH_F_SEARCH_SMALL_LISTS 0x40  /* oth_rollout, tests only: the lane-cooperative maximin search (depth >= 3) keeps at
+                                           most 3 root moves, so its per-thread fallback runs constantly */
 
 /* observation layouts (plane count P, each plane S*S cells, env-major [B][P][S][S]) */
 #define OTH_OBS_NONE        0

@@ -29,5 +29,8 @@ echo "== ncu launch list (whole short run)"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline --e2e-steps 3 > $OUT/ncu_launches.log 2>&1; echo "rc=$?"
 echo "== ncu full of the headline kernel"
 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:k_step -s 19 -c 1 -o $OUT/prof_step_8 python scripts/profile_targets.py step --size 8 > $OUT/ncu_full.log 2>&1; echo "rc=$?"
+echo "== ncu full of the maximin-2 tournament kernel"
+ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k regex:k_rollout -s 1 -c 1 -o $OUT/prof_rollout_gm2 python scripts/profile_targets.py rollout --pairing greedy_vs_maximin2 --games 262144 > $OUT/ncu_full_rollout.log 2>&1; echo "rc=$?"
+echo "== search bench"; python scripts/bench_search.py > $OUT/search.jsonl 2> $OUT/search.err; echo "rc=$?"
 echo "== ncu counters"; bash scripts/gpu_counts.sh $TAG
 ls $OUT
