@@ -21,14 +21,16 @@
 #pragma once
 #include "oth_core.cuh"
 
-constexpr int COOP_CAP1 = 32;
+constexpr int COOP_CAP1 = 32;       // depth 4: root moves of the ONE game being searched
+constexpr int COOP_CAPN = 256;      // depth 3: level-1 nodes of ALL games of a batch (32 games x ~10 root moves fit twice over)
 constexpr int COOP_INF = 0x3FFFFFFF;
 
-// per warp: the level-1 list of the game being searched (depth >= 3); depth 2 uses val / first per GAME LANE
+// per warp: the level-1 node list (depth >= 3); depth 2 uses val / first per GAME LANE
 struct CoopScratch {
-    u64 pl[COOP_CAP1], op[COOP_CAP1], mv[COOP_CAP1];   // side to move, other side, its legal moves
-    int val[COOP_CAP1];
-    short first[COOP_CAP1 + 2];                        // exclusive prefix sums of the move counts
+    u64 pl[COOP_CAPN], op[COOP_CAPN], mv[COOP_CAPN];   // side to move, other side, its legal moves
+    int val[COOP_CAPN];
+    short first[COOP_CAPN + 2];                        // exclusive prefix sums of the move counts
+    short gfirst[34];                                  // depth 3: first node of every game (lane) of the batch
 };
 
 // exclusive prefix sum of x over the warp, and the total
@@ -168,6 +170,98 @@ OTH_DEV int coop_search3(u64 P, u64 O, u64 M, bool top_is_me, CoopScratch &sc, i
     return bv;
 }
 
+// ---- depth 3, every needing game of the warp at once ----------------------------------------------------------------
+// Level 1: the root moves of all games of a batch are numbered through the warp and dealt round-robin (one lane = one
+// (game, root move): apply it, compute the reply set); level 2: the (node, reply) pairs of the whole batch in equal
+// consecutive chunks, each pair scored one ply deep and folded into its node with atomicMin; then every lane takes the
+// first maximum over ITS game's nodes.  A batch = as many games, in lane order, as fit `cap` level-1 nodes; a game
+// with more root moves than that is searched by its own lane alone (per-thread DFS).
+template <int S>
+OTH_DEV int coop_pick_depth3(bool need, u64 own, u64 opp, u64 moves, CoopScratch &sc, int cap) {
+    const int lane = threadIdx.x & 31;
+    const int n1 = need ? __popcll(moves) : 0;
+    int result = -1;
+    bool pending = n1 > 0;
+    if (pending && n1 > cap) {                                       // never on 8x8 with the real capacity
+        BB<1> o, p, mm;
+        o.w[0] = own; p.w[0] = opp; mm.w[0] = moves;
+        result = MaxiMin<S, 3>::pick(o, p, mm);
+        pending = false;
+    }
+    while (__any_sync(0xFFFFFFFFu, pending)) {                       // warp-uniform
+        // the batch: pending games in lane order while their root moves fit
+        int total;
+        const int start = coop_excl_scan(pending ? n1 : 0, lane, total);
+        const bool mine = pending && start + n1 <= cap;              // a prefix of the pending games (counts are > 0)
+        const int T1 = __reduce_max_sync(0xFFFFFFFFu, mine ? start + n1 : 0);
+        sc.gfirst[lane] = (short)min(start, T1);
+        if (lane == 0) sc.gfirst[32] = (short)T1;
+        __syncwarp();
+        // level 1
+        int run = 0;                                                 // reply pairs before this round's nodes
+        for (int q0 = 0; q0 < T1; q0 += 32) {
+            const int q = q0 + lane;
+            const bool on = q < T1;
+            const int g = on ? coop_find_node(sc.gfirst, 32, q) : 0;
+            const u64 P = __shfl_sync(0xFFFFFFFFu, own, g), O = __shfl_sync(0xFFFFFFFFu, opp, g);
+            const u64 M = __shfl_sync(0xFFFFFFFFu, moves, g);
+            int cnt = 0;
+            if (on) {
+                const u64 mv = 1ull << nth_bit64(M, q - sc.gfirst[g]);
+                const u64 f = flips1<S>(mv, P, O);
+                const u64 cpl = O & ~f, cop = P | f | mv;            // the opponent moves next
+                const u64 L = legal1<S>(cpl, cop);
+                sc.pl[q] = cpl; sc.op[q] = cop; sc.mv[q] = L;
+                sc.val[q] = (L == 0ull) ? __popcll(cop) : COOP_INF;  // no reply: a leaf (simple_policies.py:139-144)
+                cnt = __popcll(L);
+            }
+            int round_total;
+            const int ex = coop_excl_scan(cnt, lane, round_total);
+            if (on) sc.first[q] = (short)(run + ex);
+            run += round_total;
+        }
+        if (lane == 0) sc.first[T1] = (short)run;
+        __syncwarp();
+        // level 2
+        {
+            const int T2 = run;
+            const int chunk = (T2 + 31) >> 5;
+            const int q0 = min(lane * chunk, T2), q1 = min(q0 + chunk, T2);
+            if (q0 < q1) {
+                int p = coop_find_node(sc.first, T1, q0);
+                u64 pl = sc.pl[p], op = sc.op[p];
+                u64 m = coop_drop_lowest(sc.mv[p], q0 - sc.first[p]);
+                int best = COOP_INF;
+                for (int q = q0; q < q1; q++) {
+                    while (m == 0ull) {
+                        atomicMin(&sc.val[p], best);
+                        p++; pl = sc.pl[p]; op = sc.op[p]; m = sc.mv[p];
+                        best = COOP_INF;
+                    }
+                    const u64 mv = m & (0ull - m);
+                    m &= m - 1ull;
+                    const u64 f = flips1<S>(mv, pl, op);
+                    best = min(best, coop_one_ply<S>(op & ~f, pl | f | mv, true));   // the searching side moves again
+                }
+                atomicMin(&sc.val[p], best);
+            }
+            __syncwarp();
+        }
+        // every game of the batch: first maximum over its root moves (np.argmax, :151-155)
+        if (mine) {
+            int bv = -1, bi = 0;
+            for (int j = 0; j < n1; j++) {
+                const int v = sc.val[start + j];
+                if (v > bv) { bv = v; bi = j; }
+            }
+            result = nth_bit64(moves, bi);
+            pending = false;
+        }
+        __syncwarp();                                                // the lists are reused by the next batch
+    }
+    return result;
+}
+
 // MaxiMinPolicy.get_action (depth 3 or 4) for one game by the whole warp (warp-uniform arguments): the chosen action.
 template <int S, int D>
 OTH_DEV int coop_pick_one(u64 own, u64 opp, u64 moves, CoopScratch &sc, int lane, int cap1) {
@@ -208,6 +302,8 @@ __device__ __noinline__ int coop_maximin_pick(bool need, u64 own, u64 opp, u64 m
     static_assert(Geo<S>::W == 1, "cooperative search: single-word boards");
     if constexpr (D == 2) {
         return coop_pick_depth2<S>(need, own, opp, moves, sc);
+    } else if constexpr (D == 3) {
+        return coop_pick_depth3<S>(need, own, opp, moves, sc, small_lists ? 8 : COOP_CAPN);   // OTH_F_SEARCH_SMALL_LISTS
     } else {
         const int lane = threadIdx.x & 31;
         u32 todo = __ballot_sync(0xFFFFFFFFu, need);
