@@ -742,6 +742,91 @@ OTH_DEV StepResult env_step(EnvRegs<S> &e, i64 action, int flags) {
     return r;
 }
 
+// ---- multi-word boards (S = 9..16): the flip count of every cell at once, on whole-board arithmetic ------------
+// The scheme of flip_planes1 with BB<W> operands: run lengths reach S-2 <= 14 (four planes per direction, and per
+// axis: the two directions of a line still sum to <= S-2), the four axes add up to <= 4(S-2) <= 56 (six planes).
+// Not inlined: one copy per board size (about 1 000 instructions per 64-bit word), called by greedy and by the last
+// ply of the searches.
+#ifndef OTH_MW_PLANES
+#define OTH_MW_PLANES 1      // 0: multi-word boards score one move at a time (A/B builds)
+#endif
+template <int W> OTH_DEV BB<W> bb_maj(const BB<W> &a, const BB<W> &b, const BB<W> &c) { return (a & b) | (c & (a | b)); }
+template <int W> struct FlipPlanesW { BB<W> c[6]; };
+template <int S, int D, bool UP>
+OTH_DEV void run_planes(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &m, BB<Geo<S>::W> *b) {
+    constexpr int W = Geo<S>::W, R = S - 2;
+    BB<W> t = sh<D, UP, W>(P) & m;                        // t = the k-th disc of a run, k = 1
+    b[0] = t; b[1] = bb_zero<W>(); b[2] = b[1]; b[3] = b[1];
+#pragma unroll
+    for (int k = 2; k <= R; k++) {
+        t = sh<D, UP, W>(t) & m;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if ((k >> j) & 1) b[j] = b[j] | t;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) b[j] = sh<D, UP, W>(b[j]);
+}
+// o = a + b over NA planes each; the carry out becomes plane NA when NO > NA
+template <int W, int NA, int NO>
+OTH_DEV void planes_add(const BB<W> *a, const BB<W> *b, BB<W> *o) {
+    BB<W> c = a[0] & b[0];
+    o[0] = a[0] ^ b[0];
+#pragma unroll
+    for (int i = 1; i < NA; i++) {
+        o[i] = a[i] ^ b[i] ^ c;
+        if (i + 1 < NA || NO > NA) c = bb_maj<W>(a[i], b[i], c);
+    }
+    if constexpr (NO > NA) o[NA] = c;
+}
+template <int S, int D>
+OTH_DEV void axis_planes(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &m, BB<Geo<S>::W> *s) {
+    constexpr int W = Geo<S>::W;
+    BB<W> a[4], b[4];
+    run_planes<S, D, true>(P, m, a);
+    run_planes<S, D, false>(P, m, b);
+    planes_add<W, 4, 4>(a, b, s);
+}
+template <int S>
+__device__ __noinline__ FlipPlanesW<Geo<S>::W> flip_planes(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &O) {
+    constexpr int W = Geo<S>::W;
+    const BB<W> Oi = O & geo_inner<S>();
+    BB<W> h[4], v[4], x[5], y[5];
+    axis_planes<S, 1>(P, Oi, h);
+    axis_planes<S, S>(P, O, v);
+    planes_add<W, 4, 5>(h, v, x);
+    axis_planes<S, S + 1>(P, Oi, h);
+    axis_planes<S, S - 1>(P, Oi, v);
+    planes_add<W, 4, 5>(h, v, y);
+    FlipPlanesW<W> f;
+    planes_add<W, 5, 6>(x, y, f.c);
+    return f;
+}
+// the largest count among the cells of `cand`; cand shrinks to the cells that reach it
+template <int W>
+OTH_DEV int planes_max(const FlipPlanesW<W> &f, BB<W> &cand) {
+    int v = 0;
+#pragma unroll
+    for (int p = 5; p >= 0; p--) {
+        const BB<W> t = cand & f.c[p];
+        if (any(t)) { cand = t; v |= 1 << p; }
+    }
+    return v;
+}
+// legal moves of P (as legal<S>) and the most discs any of them turns (0 when there is no move), any board size
+template <int S>
+OTH_DEV int max_flips(const BB<Geo<S>::W> &P, const BB<Geo<S>::W> &O, BB<Geo<S>::W> &moves) {
+    constexpr int W = Geo<S>::W;
+    if constexpr (W == 1) {
+        return max_flips1<S>(P.w[0], O.w[0], moves.w[0]);
+    } else {
+        const FlipPlanesW<W> f = flip_planes<S>(P, O);
+        moves = andnot((f.c[0] | f.c[1] | f.c[2] | f.c[3] | f.c[4] | f.c[5]) & geo_full<S>(), P | O);
+        BB<W> cand = moves;
+        return planes_max<W>(f, cand);
+    }
+}
+
 // RandomPolicy.get_action / the opening override: uniform over the cached list
 // (simple_policies.py:37-41, othello.py:70-72)
 template <int S>
@@ -767,6 +852,15 @@ OTH_DEV int greedy_pick(const BB<Geo<S>::W> &own, const BB<Geo<S>::W> &opp, BB<G
             return __ffsll((long long)cand) - 1;           // np.argmax: the first (lowest) of the best moves
         }
     }
+    if constexpr (W > 1 && OTH_MW_PLANES) {
+        if (!any(moves & (own | opp))) {
+            if (!any(moves)) return -1;
+            const FlipPlanesW<W> f = flip_planes<S>(own, opp);
+            BB<W> cand = moves;
+            planes_max<W>(f, cand);
+            return lowest_bit(cand);
+        }
+    }
     int best = -1, best_cnt = -1;
     while (any(moves)) {
         int a = lowest_bit(moves);
@@ -786,10 +880,10 @@ struct MaxiMin {
         constexpr int W = Geo<S>::W;
         if constexpr (D == 0) {
             return popc(me_is_pl ? pl : op);
-        } else if constexpr (D == 1 && W == 1) {          // children are leaves: every move scored at once
-            u64 moves;
-            const int k = max_flips1<S>(pl.w[0], op.w[0], moves);
-            if (moves == 0ull) return popc(me_is_pl ? pl : op);
+        } else if constexpr (D == 1 && (W == 1 || OTH_MW_PLANES)) {   // children are leaves: every move scored at once
+            BB<W> moves;
+            const int k = max_flips<S>(pl, op, moves);
+            if (!any(moves)) return popc(me_is_pl ? pl : op);
             return me_is_pl ? popc(pl) + k + 1 : popc(op) - k;
         } else {
             BB<W> moves = legal<S>(pl, op);

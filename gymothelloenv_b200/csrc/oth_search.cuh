@@ -28,13 +28,13 @@ struct AlphaBeta {
     static __device__ __noinline__ int value(const BB<Geo<S>::W> &pl, const BB<Geo<S>::W> &op, bool me_is_pl, int alpha,
                                              int beta, bool prune, unsigned long long &nodes) {
         constexpr int W = Geo<S>::W;
-        if constexpr (R == 1 && W == 1) {
-            // children are leaves: all of them are scored at once (flip_planes1) -- the exact value of the node, which
+        if constexpr (R == 1 && (W == 1 || OTH_MW_PLANES)) {
+            // children are leaves: all of them are scored at once (max_flips) -- the exact value of the node, which
             // a cut-off could only have replaced by a bound on the same side of the window
-            u64 mv;
-            const int k = max_flips1<S>(pl.w[0], op.w[0], mv);
-            if (mv == 0ull) return popc(me_is_pl ? pl : op);
-            nodes += (unsigned long long)__popcll(mv);
+            BB<W> mv;
+            const int k = max_flips<S>(pl, op, mv);
+            if (!any(mv)) return popc(me_is_pl ? pl : op);
+            nodes += (unsigned long long)popc(mv);
             return me_is_pl ? popc(pl) + k + 1 : popc(op) - k;
         }
         BB<W> moves = legal_ni<S>(pl, op);

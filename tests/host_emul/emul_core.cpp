@@ -92,27 +92,35 @@ static void nth_batch(int64_t B, const uint64_t *legal_, const int32_t *n, int64
     }
 }
 
-// bit-sliced flip counts (flip_planes1 / max_flips1) next to the per-move flips1 + legal1 they replace
+// bit-sliced flip counts (flip_planes1 / flip_planes / max_flips) next to the per-move flips_at + legal they replace;
+// boards are [W][B] words, counts [B][64*W]
 template <int S>
 static void flipcount_batch(int64_t B, const uint64_t *own, const uint64_t *opp, int8_t *sliced, int8_t *per_move,
-                            uint64_t *moves_sliced, uint64_t *moves_legal1, int32_t *max_sliced) {
-    if constexpr (Geo<S>::W == 1) {
-        constexpr int N = Geo<S>::N;
-        for (int64_t i = 0; i < B; i++) {
-            const u64 P = own[i], O = opp[i];
-            const FlipPlanes f = flip_planes1<S>(P, O);
-            for (int a = 0; a < 64; a++) {
-                int c = 0;
-                for (int p = 0; p < 5; p++) c |= (int)((f.c[p] >> a) & 1ull) << p;
-                const bool empty = a < N && !(((P | O) >> a) & 1ull);
-                sliced[i * 64 + a] = (int8_t)(empty ? c : -1);
-                per_move[i * 64 + a] = (int8_t)(empty ? __popcll(flips1<S>(1ull << a, P, O)) : -1);
-            }
-            u64 mv;
-            max_sliced[i] = max_flips1<S>(P, O, mv);
-            moves_sliced[i] = mv;
-            moves_legal1[i] = legal1<S>(P, O);
+                            uint64_t *moves_sliced, uint64_t *moves_legal, int32_t *max_sliced) {
+    constexpr int N = Geo<S>::N, W = Geo<S>::W;
+    for (int64_t i = 0; i < B; i++) {
+        BB<W> P, O;
+        for (int k = 0; k < W; k++) { P.w[k] = own[k * B + i]; O.w[k] = opp[k * B + i]; }
+        uint64_t plane[6][W];
+        if constexpr (W == 1) {
+            const FlipPlanes f = flip_planes1<S>(P.w[0], O.w[0]);
+            for (int p = 0; p < 5; p++) plane[p][0] = f.c[p];
+            plane[5][0] = 0;
+        } else {
+            const FlipPlanesW<W> f = flip_planes<S>(P, O);
+            for (int p = 0; p < 6; p++) for (int k = 0; k < W; k++) plane[p][k] = f.c[p].w[k];
         }
+        for (int a = 0; a < 64 * W; a++) {
+            int c = 0;
+            for (int p = 0; p < 6; p++) c |= (int)((plane[p][a >> 6] >> (a & 63)) & 1ull) << p;
+            const bool empty = a < N && !(((P.w[a >> 6] | O.w[a >> 6]) >> (a & 63)) & 1ull);
+            sliced[i * 64 * W + a] = (int8_t)(empty ? c : -1);
+            per_move[i * 64 * W + a] = (int8_t)(empty ? popc(flips_at<S>(a, bb_bit<W>(a), P, O)) : -1);
+        }
+        BB<W> mv;
+        max_sliced[i] = max_flips<S>(P, O, mv);
+        const BB<W> lg = legal<S>(P, O);
+        for (int k = 0; k < W; k++) { moves_sliced[k * B + i] = mv.w[k]; moves_legal[k * B + i] = lg.w[k]; }
     }
 }
 
@@ -161,7 +169,6 @@ int emul_nth(int S, int64_t B, const uint64_t *legal_, const int32_t *n, int64_t
 }
 int emul_flipcount(int S, int64_t B, const uint64_t *own, const uint64_t *opp, int8_t *sliced, int8_t *per_move,
                    uint64_t *moves_sliced, uint64_t *moves_legal1, int32_t *max_sliced) {
-    if (S > 8) return -1;
 #define CALL(N) flipcount_batch<N>(B, own, opp, sliced, per_move, moves_sliced, moves_legal1, max_sliced)
     DISPATCH(S, CALL)
 #undef CALL

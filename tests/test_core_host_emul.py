@@ -176,26 +176,75 @@ def test_alpha_beta_search_matches_oracle_maximin(emul, S, depths):
     assert checked > 20
 
 
-@pytest.mark.parametrize("S", [4, 5, 6, 7, 8])
+@pytest.mark.parametrize("S", [4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 16])
 def test_bit_sliced_flip_counts_equal_per_move_flips(emul, S):
-    """flip_planes1 / max_flips1 (every move scored at once: greedy and the last ply of the searches) against one
-    flips1 + popcount per cell and legal1, on ARBITRARY disc patterns -- sparse, dense, reachable or not."""
+    """flip_planes1 / flip_planes / max_flips (every move scored at once: greedy and the last ply of the searches)
+    against one flips_at + popcount per cell and legal<S>, on ARBITRARY disc patterns -- sparse, dense, reachable or
+    not -- including long runs (rows / columns / diagonals filled with one colour)."""
     rng = np.random.RandomState(100 + S)
-    N, B = S * S, 6000
+    N, W = S * S, (S * S + 63) // 64
+    B = 6000 if W == 1 else 1500
     fill = rng.choice([0.15, 0.4, 0.7, 0.95], size=B)
     cells = rng.rand(B, N)
-    colour = rng.rand(B, N) < rng.choice([0.2, 0.5, 0.8], size=(B, 1))
+    colour = rng.rand(B, N) < rng.choice([0.1, 0.2, 0.5, 0.8], size=(B, 1))
     occupied = cells < fill[:, None]
-    weights = (np.uint64(1) << np.arange(N, dtype=np.uint64))
-    own = ((occupied & colour).astype(np.uint64) * weights).sum(1).astype(np.uint64)
-    opp = ((occupied & ~colour).astype(np.uint64) * weights).sum(1).astype(np.uint64)
-    sliced, per_move = np.zeros((B, 64), dtype=np.int8), np.zeros((B, 64), dtype=np.int8)
-    mv_s, mv_l, mx = np.zeros(B, dtype=np.uint64), np.zeros(B, dtype=np.uint64), np.zeros(B, dtype=np.int32)
+    ownc, oppc = occupied & colour, occupied & ~colour
+    dense = np.zeros((2, B, 64 * W), dtype=np.uint64)
+    dense[0, :, :N], dense[1, :, :N] = ownc, oppc
+    weights = (np.uint64(1) << np.arange(64, dtype=np.uint64))
+    words = (dense.reshape(2, B, W, 64) * weights).sum(3).astype(np.uint64)          # (2, B, W)
+    own, opp = np.ascontiguousarray(words[0].T), np.ascontiguousarray(words[1].T)    # [W][B]
+    sliced, per_move = np.zeros((B, 64 * W), dtype=np.int8), np.zeros((B, 64 * W), dtype=np.int8)
+    mv_s, mv_l = np.zeros((W, B), dtype=np.uint64), np.zeros((W, B), dtype=np.uint64)
+    mx = np.zeros(B, dtype=np.int32)
     assert emul.emul_flipcount(S, C.c_int64(B), _p(own), _p(opp), _p(sliced), _p(per_move), _p(mv_s), _p(mv_l), _p(mx)) == 0
     assert np.array_equal(sliced, per_move)
     assert np.array_equal(mv_s, mv_l)
     assert np.array_equal(mx, per_move.max(1).clip(min=0))
-    assert per_move.max() >= min(2 * (S - 2), 8) and (mv_s != 0).mean() > 0.3      # the cases are not trivial
+    assert per_move.max() >= min(2 * (S - 2), 8) and (mv_s != 0).any(0).mean() > 0.3      # the cases are not trivial
+
+
+@pytest.mark.parametrize("S", [6, 8, 10, 12, 13, 16])
+def test_bit_sliced_flip_counts_on_star_patterns(emul, S):
+    """One empty cell with a bracketed opponent run of a chosen length in each of the 8 directions (up to the longest
+    the board allows): the large sums and every carry of the bit-sliced adders, which random boards rarely reach."""
+    rng = np.random.RandomState(7 + S)
+    N, W, B = S * S, (S * S + 63) // 64, 800
+    own_c, opp_c = np.zeros((B, N), dtype=bool), np.zeros((B, N), dtype=bool)
+    want = np.zeros(B, dtype=np.int64)
+    centre = np.zeros(B, dtype=np.int64)
+    for i in range(B):
+        r0, c0 = rng.randint(S), rng.randint(S)
+        centre[i] = r0 * S + c0
+        total = 0
+        for dr, dc in ((0, 1), (0, -1), (1, 0), (-1, 0), (1, 1), (-1, -1), (1, -1), (-1, 1)):
+            room = 0                                          # cells available behind the centre in this direction
+            r, c = r0 + dr, c0 + dc
+            while 0 <= r < S and 0 <= c < S:
+                room += 1
+                r, c = r + dr, c + dc
+            if room < 2:
+                continue
+            k = room - 1 if rng.rand() < 0.6 else rng.randint(0, room)      # mostly the longest run
+            closed = rng.rand() < 0.85
+            for j in range(1, k + 1):
+                opp_c[i, (r0 + j * dr) * S + c0 + j * dc] = True
+            if closed and k > 0:
+                own_c[i, (r0 + (k + 1) * dr) * S + c0 + (k + 1) * dc] = True
+                total += k
+        want[i] = total
+    dense = np.zeros((2, B, 64 * W), dtype=np.uint64)
+    dense[0, :, :N], dense[1, :, :N] = own_c, opp_c
+    weights = (np.uint64(1) << np.arange(64, dtype=np.uint64))
+    words = (dense.reshape(2, B, W, 64) * weights).sum(3).astype(np.uint64)
+    own, opp = np.ascontiguousarray(words[0].T), np.ascontiguousarray(words[1].T)
+    sliced, per_move = np.zeros((B, 64 * W), dtype=np.int8), np.zeros((B, 64 * W), dtype=np.int8)
+    mv_s, mv_l = np.zeros((W, B), dtype=np.uint64), np.zeros((W, B), dtype=np.uint64)
+    mx = np.zeros(B, dtype=np.int32)
+    assert emul.emul_flipcount(S, C.c_int64(B), _p(own), _p(opp), _p(sliced), _p(per_move), _p(mv_s), _p(mv_l), _p(mx)) == 0
+    assert np.array_equal(sliced, per_move) and np.array_equal(mv_s, mv_l)
+    assert np.array_equal(sliced[np.arange(B), centre], want)             # the construction itself
+    assert want.max() >= 3 * (S - 3)                                       # sums well into the upper planes
 
 
 def test_nth_set_bit(emul):
