@@ -10,14 +10,16 @@
 //   depth 2   items = the root moves of ALL games of the warp that need a decision, numbered through the warp
 //             (prefix sum of the move counts) and dealt round-robin to the 32 lanes; a game's best (value, lowest
 //             move) is folded with one shared-memory atomicMax per item on a packed key
-//   depth 3   one game at a time: one lane per root move builds the reply list (level 1: position + reply set),
-//             then the (root move, reply) pairs are split into equal consecutive chunks over the lanes and each
-//             pair's value is folded into its root move with atomicMin; the root takes the first argmax
-//   depth 4   the root's moves in sequence, each searched to depth 3 cooperatively (roles swapped)
+//   depth 3   the same pooling on two levels: the root moves of a batch of games are dealt round-robin (one lane = one
+//             (game, root move): apply it, compute the reply set -> level-1 node list in shared memory), then the
+//             (node, reply) pairs of the whole batch are split into equal consecutive chunks over the lanes and each
+//             pair's value is folded into its node with atomicMin; every lane takes the first argmax of ITS game
+//   depth 4   the root's moves in sequence, each searched to depth 3 by the whole warp (roles swapped), one game at
+//             a time
 // Values only travel upwards through min / max, so the result does not depend on the order of evaluation; the one
 // place where ties matter is the root (np.argmax first occurrence, :151-155), reduced with (value, lowest index).
-// More than COOP_CAP1 root moves (never seen on 8x8): that decision falls back to the per-thread DFS;
-// OTH_F_SEARCH_SMALL_LISTS shrinks the limit so that the tests run the fallback constantly.
+// More root moves in one position than the lists hold (never seen on 8x8): that decision falls back to the per-thread
+// DFS; OTH_F_SEARCH_SMALL_LISTS shrinks the limits so that the tests run batching and fallback constantly.
 #pragma once
 #include "oth_core.cuh"
 
