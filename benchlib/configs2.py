@@ -193,7 +193,7 @@ def run_scalar(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
             "config": {"workload": "8x8 random vs greedy, 100 games, first 10 moves random (run.py --no-render), "
                                    "configs[0], ONE env stepped through the Gym API",
-                       "note": "a B=1 env is a launch-latency workload (several launches + one D2H sync per step()); "
+                       "note": "a B=1 env is a launch-latency workload (one or two launches that write pinned host memory + one stream sync per call); "
                                "the batched API is the product, this line reports the drop-in honestly"},
             "scalar_api": {"games": games, "seconds": dt, "plies": plies, "plies_per_s": plies / dt, "black_wdl": tally},
             "batched_same_protocol": {"games": 1 << 20, "ms": ms, "games_per_s": (1 << 20) / (ms * 1e-3),
@@ -201,8 +201,8 @@ def run_scalar(args):
             "roofline": {"bound": "latency", "achieved": None, "peak": None, "unit": None, "frac": None, "traffic": None,
                          "note": "one env per launch: bounded by launch + D2H sync latency, not by a throughput roofline"},
             "cpu_baseline": cpu,
-            "e2e": {"value": games / dt, "unit": "games/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 8 * 8 * 2 + 64 + 8,
-                    "note": "the scalar API IS end to end: every step() copies its action in and obs / mask / scalars out"},
+            "e2e": {"value": games / dt, "unit": "games/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 8 * 8 * 2 + 16 + 256 + 8,
+                    "note": "the scalar API IS end to end: every step() reads its action from and writes obs / mask / record / planes to pinned host memory"},
             "gpu_launches": None, "clocks": None,
         })
     ranks.finish()

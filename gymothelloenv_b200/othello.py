@@ -68,14 +68,26 @@ class OthelloBaseEnv(object):
                                   obs_layout="board+mask" if possible_actions_in_obs else "board",
                                   obs_dtype=torch.int8)
         S, N = self.board_size, self.board_size ** 2
-        self._abs_dev = torch.zeros((1, S, S), dtype=torch.int8, device=self._vec.device)
-        self._action_dev = torch.zeros((1,), dtype=torch.int64, device=self._vec.device)
-        # pinned host mirrors, refreshed by ONE synchronisation per call
-        self._h_abs = torch.zeros((S, S), dtype=torch.int8).pin_memory()
-        self._h_obs = torch.zeros(tuple(self._vec.obs.shape[1:]), dtype=torch.int8).pin_memory()
+        # Host mirrors in PINNED memory, which the device addresses directly (unified addressing): the kernels of a
+        # scalar call write obs / legal mask / the 16-byte result record / the make_state planes straight into them and
+        # read the action from one, so a call is kernel launches + ONE stream synchronisation -- no memcpy, no
+        # per-call device tensor.  (A B = 1 env is a launch-latency workload; this is what its latency is made of.)
+        v = self._vec
+        self._h_obs = torch.zeros(tuple(v.obs.shape[1:]), dtype=torch.int8).pin_memory()
         self._h_mask = torch.zeros((N,), dtype=torch.uint8).pin_memory()
-        self._h_meta = torch.zeros((1,), dtype=torch.int32).pin_memory()
-        self._h_reward = torch.zeros((1,), dtype=torch.float32).pin_memory()
+        self._h_packed = torch.zeros((16,), dtype=torch.uint8).pin_memory()
+        self._h_planes = torch.zeros((4, S, S), dtype=torch.int8).pin_memory()
+        self._h_action = torch.zeros((1,), dtype=torch.int64).pin_memory()
+        self._h_pick = torch.zeros((1,), dtype=torch.int64).pin_memory()
+        self._np_obs, self._np_mask, self._np_planes = self._h_obs.numpy(), self._h_mask.numpy(), self._h_planes.numpy()
+        self._np_reward = self._h_packed.view(torch.float32).numpy()          # record: f32 reward | done | turn | winner
+        self._np_status = self._h_packed.view(torch.int8).numpy()
+        none5 = (None,) * 5
+        self._c_host_out = _cabi.OthOutputs(_cabi.ptr(self._h_obs), _cabi.ptr(self._h_mask), *none5,
+                                            _cabi.OBS_BOARD_MASK if possible_actions_in_obs else _cabi.OBS_BOARD,
+                                            _cabi.DTYPE_I8, _cabi.ptr(self._h_packed))
+        self._c_host_planes = _cabi.OthOutputs(_cabi.ptr(self._h_planes), None, *none5, _cabi.OBS_PLANES4, _cabi.DTYPE_I8)
+        self._action_dev = torch.zeros((1,), dtype=torch.int64, device=v.device)
 
         # internal state as in the reference right after __init__ (othello.py:232,239-242)
         self._vec.reset()
@@ -87,24 +99,49 @@ class OthelloBaseEnv(object):
         self.observation_space = Box(np.zeros(shape), np.ones(shape))
 
     # ------------------------------------------------------------------ device <-> host
-    def _pull(self):
-        """Mirror the device state: board_state, player_turn, winner, terminated, possible_moves, obs."""
+    def _sync_host(self):
+        """Waits for the kernels that wrote the host mirrors and decodes them: board_state, player_turn, winner,
+        terminated, possible_moves, obs."""
+        torch.cuda.current_stream(self._vec.device).synchronize()
+        st = self._np_status
+        self.terminated = bool(st[4])
+        self.player_turn = WHITE_DISK if st[5] > 0 else BLACK_DISK
+        self.winner = int(st[6])
+        obs = self._np_obs.astype(np.int64)
+        self._obs_host = obs
+        mover_view = obs[0] if obs.ndim == 3 else obs                         # the mover's discs are +1 (othello.py:363-369)
+        self.board_state = mover_view * self.player_turn                      # int board like np.zeros(dtype=int)
+        self.possible_moves = np.flatnonzero(self._np_mask).tolist()
+
+    def _emit_planes(self):
         v = self._vec
-        v.observe("absolute", torch.int8, out=self._abs_dev)
-        self._h_abs.copy_(self._abs_dev[0], non_blocking=True)
-        self._h_obs.copy_(v.obs[0], non_blocking=True)
-        self._h_mask.copy_(v._mask_u8[0], non_blocking=True)
-        self._h_meta.copy_(v._meta, non_blocking=True)
-        self._h_reward.copy_(v.reward, non_blocking=True)
-        torch.cuda.current_stream(v.device).synchronize()
-        meta = int(self._h_meta[0])
-        self.board_state = self._h_abs.numpy().astype(np.int64)                # int board like np.zeros(dtype=int)
-        self.player_turn = WHITE_DISK if meta & _cabi.META_TURN_WHITE else BLACK_DISK
-        self.terminated = bool(meta & _cabi.META_TERMINATED)
-        code = (meta >> _cabi.META_WINNER_SHIFT) & 3
-        self.winner = WHITE_DISK if code == 1 else (BLACK_DISK if code == 2 else NO_DISK)
-        self.possible_moves = np.nonzero(self._h_mask.numpy())[0].tolist()
-        self._obs_host = self._h_obs.numpy().astype(np.int64)
+        _cabi.check(v._lib.oth_observe(v._state(), 1, self.board_size, v._flags(), self._c_host_planes, v._stream()),
+                    "oth_observe")
+
+    def _pull(self):
+        """Mirror the device state (after anything but step() changed it)."""
+        v = self._vec
+        with v._on_device():
+            _cabi.check(v._lib.oth_observe(v._state(), 1, self.board_size, v._flags(), self._c_host_out, v._stream()),
+                        "oth_observe")
+            self._emit_planes()
+        self._sync_host()
+
+    def current_planes(self):
+        """util.make_state's four planes of the CURRENT state (int8 (4,S,S), written by the device with every call)."""
+        return self._np_planes
+
+    def device_pick(self, kind, depth):
+        """policy.get_action on the device state: one oth_policy launch writing the action into pinned memory."""
+        from .vec_env import policy_spec
+        v = self._vec
+        with v._on_device():
+            _cabi.check(v._lib.oth_policy(v._state(), 1, self.board_size, policy_spec(kind, depth), v.seed_value,
+                                          v._policy_counter, v.env_id_base, _cabi.ptr(self._h_pick), v._stream()),
+                        "oth_policy")
+            v._policy_counter += 1
+            torch.cuda.current_stream(v.device).synchronize()
+        return int(self._h_pick[0])
 
     def _push_board(self):
         """board_state may have been assigned by the caller: send it to the device."""
@@ -186,11 +223,16 @@ class OthelloBaseEnv(object):
             a = -1
         if not (-(1 << 62) < a < (1 << 62)):
             a = -1
-        self._action_dev.fill_(a)
-        self._vec.step(self._action_dev)
+        v = self._vec
+        self._h_action[0] = a
         was_terminated = self.terminated
-        self._pull()
-        reward = int(self._h_reward[0])
+        with v._on_device():
+            _cabi.check(v._lib.oth_step(v._state(), 1, self.board_size, v._flags(), _cabi.ACT_EXTERNAL,
+                                        _cabi.ptr(self._h_action), v.seed_value, v.env_id_base, v.initial_rand_steps,
+                                        self._c_host_out, v._stream()), "oth_step")
+            self._emit_planes()
+        self._sync_host()
+        reward = int(self._np_reward[0])
         if self.terminated and not was_terminated and not self.mute:
             self._announce()
         return self.get_observation(), reward, self.terminated, None

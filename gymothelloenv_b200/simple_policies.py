@@ -85,6 +85,8 @@ def _device_pick(base_env, kind, depth, obs_board=None):
             assert all(m in legal_now for m in base_env.possible_moves)      # simple_policies.py:82
             scratch._legal.copy_(vec._legal)
             vec = scratch
+    if vec is base_env._vec:
+        return base_env.device_pick(kind, depth)             # one launch, the action lands in pinned memory
     return int(vec.policy_actions(kind, depth)[0].item())
 
 

@@ -41,7 +41,9 @@ def make_state(obs, env):
         raise ValueError("make_state expects the (S,S) observation (possible_actions_in_obs=False)")
     vec = base._vec
     cur = base.board_state * base.player_turn
-    if not np.array_equal(board.astype(np.int64), cur):
+    if np.array_equal(board.astype(np.int64), cur):
+        return base.current_planes().astype(np.float64)      # written by the device with the env's last call
+    else:
         scratch = base._scratch()
         scratch.set_board_state(board.astype(np.int8).reshape(1, -1), perspective=base.player_turn,
                                 turn=base.player_turn, recompute_legal=False)
