@@ -17,6 +17,10 @@
 #endif
 constexpr int OTH_BLOCK = 128;
 constexpr int OTH_WARPS = OTH_BLOCK / 32;
+constexpr int OTH_BLOCK_SMALL = 64;   // CTA size of the step kernels for batches that leave an SM only a few CTAs
+#ifndef OTH_SMALL_BATCH_CTAS_PER_SM
+#define OTH_SMALL_BATCH_CTAS_PER_SM 8  // half-size CTAs are considered below this many 128-env CTAs per SM (0: never)
+#endif
 
 enum { ROW_BLACK = 0, ROW_WHITE = 1, ROW_LEGAL = 2, ROW_ZERO = 3, ROW_ONES = 4, ROW_COUNT = 5 };
 #define OTH_LAYOUT_MASK_INTERNAL 6   // the dense legal_mask buffer, written with the same machinery
@@ -950,10 +954,10 @@ OTH_DEV void step_one_env(const StepParams &p, EnvRegs<S> &e, i64 i, i64 ext_act
 }
 
 // SRC: OTH_ACT_* at compile time.  General kernel: one 128-env tile per CTA, any B, any output set.
-template <int S, int SRC>
-__global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
-    __shared__ WarpStage<S> stage[OTH_WARPS];
-    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+template <int S, int SRC, int BLOCK = OTH_BLOCK>
+__global__ void __launch_bounds__(BLOCK) k_step(StepParams p) {
+    __shared__ WarpStage<S> stage[BLOCK / 32];
+    const i64 i = (i64)blockIdx.x * BLOCK + threadIdx.x;
     const bool active = i < p.B;
     EnvRegs<S> e = empty_env<S>();
     bool zero_obs = false;
@@ -969,10 +973,10 @@ __global__ void __launch_bounds__(OTH_BLOCK) k_step(StepParams p) {
 // One 128-env tile per CTA: the hardware's CTA scheduler staggers the CTAs' load / rules / store phases.  Multi-tile
 // CTAs that prefetch the next tile's state (in registers, or staged in shared memory with cp.async) were built and
 // measured: 39.7-43.8 us against 38.9 us, slower the more tiles a CTA owns (profiles/r03e_experiments.md).
-template <int S, int SRC>
-__global__ void __launch_bounds__(OTH_BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : OTH_STEPN_MIN_CTAS) k_step_fast(StepParams p) {
-    __shared__ WarpStage<S> stage[OTH_WARPS];
-    const i64 i = (i64)blockIdx.x * OTH_BLOCK + threadIdx.x;
+template <int S, int SRC, int BLOCK = OTH_BLOCK>
+__global__ void __launch_bounds__(BLOCK, S == 8 ? OTH_STEP8_MIN_CTAS : OTH_STEPN_MIN_CTAS) k_step_fast(StepParams p) {
+    __shared__ WarpStage<S> stage[BLOCK / 32];
+    const i64 i = (i64)blockIdx.x * BLOCK + threadIdx.x;
     EnvRegs<S> e;
     load_env<S>(e, p.st, i, p.B);
     bool zero_obs = false;
@@ -1596,9 +1600,30 @@ struct SizeLaunch {
             fast = p.B % OTH_BLOCK == 0 && o.packed != nullptr && o.obs != nullptr && o.legal_mask != nullptr &&
                    o.obs_layout == OTH_OBS_BOARD && o.obs_dtype == OTH_DTYPE_I8 && !o.reward && !o.done &&
                    !o.player_turn && !o.winner && !o.actions_out;
-            if (fast) k_step_fast<S, SRC><<<(unsigned)(p.B / OTH_BLOCK), OTH_BLOCK, 0, q>>>(p);
+            if (fast) {
+                if (small_batch(p.B)) k_step_fast<S, SRC, OTH_BLOCK_SMALL><<<(unsigned)(p.B / OTH_BLOCK_SMALL), OTH_BLOCK_SMALL, 0, q>>>(p);
+                else k_step_fast<S, SRC><<<(unsigned)(p.B / OTH_BLOCK), OTH_BLOCK, 0, q>>>(p);
+            }
         }
-        if (!fast) k_step<S, SRC><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        if (!fast) {
+            if (small_batch(p.B)) k_step<S, SRC, OTH_BLOCK_SMALL><<<(unsigned)((p.B + OTH_BLOCK_SMALL - 1) / OTH_BLOCK_SMALL), OTH_BLOCK_SMALL, 0, q>>>(p);
+            else k_step<S, SRC><<<oth_grid(p.B), OTH_BLOCK, 0, q>>>(p);
+        }
+    }
+    // A small batch is cut into 64-env CTAs when that lowers the load of the fullest SM: 65,536 envs are 512 CTAs of
+    // 128 on 148 SMs -- 3.46 per SM, so the SMs that get 4 (512 envs) set the time -- but 1,024 CTAs of 64 put at most
+    // 7 (448 envs) on one.  Equal loads keep 128 (measured: 32,768 and 131,072 envs are 2 % faster with 128), and so
+    // do large batches (64-thread CTAs measured 2 % slower at 2^20 envs).  profiles/r04i_small_batches.md
+    static bool small_batch(i64 B) {
+        static int sms = 0;
+        if (sms == 0) {
+            int dev = 0, n = 0;
+            if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) sms = n;
+            else sms = 148;
+        }
+        if (OTH_SMALL_BATCH_CTAS_PER_SM <= 0 || B >= (i64)sms * OTH_SMALL_BATCH_CTAS_PER_SM * OTH_BLOCK) return false;
+        const i64 big = (B + OTH_BLOCK - 1) / OTH_BLOCK, small = (B + OTH_BLOCK_SMALL - 1) / OTH_BLOCK_SMALL;
+        return ((small + sms - 1) / sms) * OTH_BLOCK_SMALL < ((big + sms - 1) / sms) * OTH_BLOCK;
     }
     static cudaError_t step(const StepParams &p0, cudaStream_t q) {
         StepParams p = p0;
