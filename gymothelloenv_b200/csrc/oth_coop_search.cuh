@@ -32,7 +32,7 @@ struct CoopScratch {
     u64 pl[COOP_CAPN], op[COOP_CAPN], mv[COOP_CAPN];   // side to move, other side, its legal moves
     int val[COOP_CAPN];
     short first[COOP_CAPN + 2];                        // exclusive prefix sums of the move counts
-    short gfirst[34];                                  // depth 3: first node of every game (lane) of the batch
+    unsigned short item[COOP_CAPN];                    // depth 3: the batch's root moves, (game lane << 6) | cell, in item order
 };
 
 // exclusive prefix sum of x over the warp, and the total
@@ -71,6 +71,14 @@ OTH_DEV int coop_one_ply(u64 cpl, u64 cop, bool cpl_is_me) {
     return __popcll(cop) - k;
 }
 
+// Every lane lists ITS game's moves at its place in the warp-wide item numbering (`first` = the exclusive prefix sum
+// of the move counts): the lane that later takes item q reads (game, cell) with one load instead of searching the
+// prefix sums and extracting the k-th set bit.
+OTH_DEV void coop_list_moves(unsigned short *item, int lane, int first, u64 moves) {
+    int q = first;
+    for (u64 m = moves; m != 0ull; m &= m - 1ull) item[q++] = (unsigned short)((lane << 6) | (__ffsll((long long)m) - 1));
+}
+
 // ---- depth 2: every needing game of the warp at once ------------------------------------------------------------
 template <int S>
 OTH_DEV int coop_pick_depth2(bool need, u64 own, u64 opp, u64 moves, CoopScratch &sc) {
@@ -78,18 +86,20 @@ OTH_DEV int coop_pick_depth2(bool need, u64 own, u64 opp, u64 moves, CoopScratch
     const int n = need ? __popcll(moves) : 0;
     int total;
     const int first = coop_excl_scan(n, lane, total);
-    sc.first[lane] = (short)first;
     sc.val[lane] = -1;
-    if (lane == 0) sc.first[32] = (short)total;
+    // the item list lies over the node arrays, which depth 2 does not use: pl + op = 2 048 entries, and 32 games have
+    // at most 32 x 60 moves between them
+    static_assert(sizeof(sc.pl) + sizeof(sc.op) >= 2 * 32 * 64, "item list capacity");
+    unsigned short *item = reinterpret_cast<unsigned short *>(sc.pl);
+    if (n > 0) coop_list_moves(item, lane, first, moves);
     __syncwarp();
     for (int q0 = 0; q0 < total; q0 += 32) {                         // warp-uniform
         const int q = q0 + lane;
         const bool on = q < total;
-        const int g = on ? coop_find_node(sc.first, 32, q) : 0;      // the game (lane) item q belongs to
+        const int it = on ? item[q] : 0;
+        const int g = it >> 6, a = it & 63;                          // the game (lane) and cell of item q
         const u64 P = __shfl_sync(0xFFFFFFFFu, own, g), O = __shfl_sync(0xFFFFFFFFu, opp, g);
-        const u64 M = __shfl_sync(0xFFFFFFFFu, moves, g);
         if (on) {
-            const int a = nth_bit64(M, q - sc.first[g]);
             const u64 mv = 1ull << a;
             const u64 f = flips1<S>(mv, P, O);
             const int v = coop_one_ply<S>(O & ~f, P | f | mv, false);
@@ -196,20 +206,19 @@ OTH_DEV int coop_pick_depth3(bool need, u64 own, u64 opp, u64 moves, CoopScratch
         const int start = coop_excl_scan(pending ? n1 : 0, lane, total);
         const bool mine = pending && start + n1 <= cap;              // a prefix of the pending games (counts are > 0)
         const int T1 = __reduce_max_sync(0xFFFFFFFFu, mine ? start + n1 : 0);
-        sc.gfirst[lane] = (short)min(start, T1);
-        if (lane == 0) sc.gfirst[32] = (short)T1;
+        if (mine) coop_list_moves(sc.item, lane, start, moves);
         __syncwarp();
         // level 1
         int run = 0;                                                 // reply pairs before this round's nodes
         for (int q0 = 0; q0 < T1; q0 += 32) {
             const int q = q0 + lane;
             const bool on = q < T1;
-            const int g = on ? coop_find_node(sc.gfirst, 32, q) : 0;
+            const int it = on ? sc.item[q] : 0;
+            const int g = it >> 6;                                   // the game (lane) of item q
             const u64 P = __shfl_sync(0xFFFFFFFFu, own, g), O = __shfl_sync(0xFFFFFFFFu, opp, g);
-            const u64 M = __shfl_sync(0xFFFFFFFFu, moves, g);
             int cnt = 0;
             if (on) {
-                const u64 mv = 1ull << nth_bit64(M, q - sc.gfirst[g]);
+                const u64 mv = 1ull << (it & 63);
                 const u64 f = flips1<S>(mv, P, O);
                 const u64 cpl = O & ~f, cop = P | f | mv;            // the opponent moves next
                 const u64 L = legal1<S>(cpl, cop);
